@@ -1,0 +1,119 @@
+/*
+ * svb.h — C ABI of the B200-native stereo depth engine (libsvb.so).
+ *
+ * The reference (jacksonroah/stereo-vision) has no FFI of its own: its dense hot path is the set of
+ * cv2 calls its helpers make (`import cv2` at the top of every script).  Each entry point below names
+ * the cv2 call it replaces and the reference call site that drives it:
+ *
+ *   svb_init_undistort_rectify_map  <- cv2.initUndistortRectifyMap(K,d,R,P,size,CV_32FC1)
+ *        stereo_calibration/scripts/checkerboard_distance.py:54-57
+ *        calibration_tests/calibrate_v4/distance.py:148-151, calibrate_v4/extrinsic.py:371-374
+ *   svb_remap_u8                    <- cv2.remap(img,map1,map2,cv2.INTER_LINEAR)
+ *        checkerboard_distance.py:71-72, calibrate_v4/distance.py:154-155, calibrate_v4/extrinsic.py:377-378
+ *   svb_sgbm_*                      <- cv2.StereoSGBM_create(**kw).compute(left,right)   (north_star; the
+ *        reference computes Q for it at checkerboard_distance.py:49-51 / calibrate_v4/extrinsic.py:312-324)
+ *   svb_median3_s16 / svb_filter_speckles_s16  <- the medianBlur(3)/filterSpeckles stages inside compute()
+ *   svb_reproject_to_3d             <- cv2.reprojectImageTo3D(disp,Q,handleMissingValues)
+ *   svb_box_median_depth            <- per-YOLO-box depth (ball_drop.py:89-160 box -> :225-259 3-D point),
+ *        re-defined on the dense map
+ *
+ * Conventions: every function returns 0 on success, <0 on error (message: svb_last_error(), thread-local).
+ * All data pointers are DEVICE pointers owned by the caller (e.g. torch tensors' data_ptr()); `stream` is a
+ * cudaStream_t passed as void* (NULL = legacy default stream).  Nothing here allocates memory the caller
+ * must free, except the context itself.  One context per (host thread, device); calls on one context are
+ * not re-entrant.  There is no CPU fallback: without a CUDA device every compute call fails.
+ */
+#ifndef SVB_H
+#define SVB_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SVB_OK 0
+#define SVB_ERR_INVALID (-1)   /* bad argument (cv2.error -215 / -2 cases)           */
+#define SVB_ERR_CUDA (-2)      /* CUDA runtime error                                  */
+#define SVB_ERR_UNSUPPORTED (-3) /* valid for cv2 but outside this engine's contract  */
+#define SVB_ERR_WORKSPACE (-4) /* caller workspace too small                          */
+
+typedef struct svb_context svb_context;
+
+/* The 11 StereoSGBM_create parameters, RAW (as the caller passed them to cv2); resolution to effective
+ * values happens inside the library — see svb_sgbm_resolve_params. */
+typedef struct svb_sgbm_params {
+    int32_t minDisparity, numDisparities, blockSize, P1, P2, disp12MaxDiff, preFilterCap, uniquenessRatio,
+        speckleWindowSize, speckleRange, mode; /* mode: 0 = MODE_SGBM (5 paths), 1 = MODE_HH (8 paths) */
+} svb_sgbm_params;
+
+/* Geometry derived from params + image width (SURVEY.md §3.2.1 "Constants"). */
+typedef struct svb_sgbm_geometry {
+    int32_t minX1, maxX1, width1; /* matched columns [minX1,maxX1)                       */
+    int32_t D, Dp;                /* numDisparities and its padded in-HBM extent          */
+    int32_t invalid16;            /* (minDisparity-1)*16                                   */
+    int32_t max_cost;             /* bound on C(p,d): bs^2 * channels * (2*ftzero+63)      */
+    int32_t safe_packed;          /* 1 if S accumulates without per-add saturation        */
+} svb_sgbm_geometry;
+
+const char *svb_last_error(void);
+const char *svb_version(void);
+
+int svb_create(int device_id, svb_context **ctx);
+int svb_destroy(svb_context *ctx);
+
+/* ---- parameter resolution (host only; no device needed) ---- */
+int svb_sgbm_resolve_params(const svb_sgbm_params *raw, svb_sgbm_params *effective);
+int svb_sgbm_get_geometry(const svb_sgbm_params *raw, int W, int channels, svb_sgbm_geometry *g);
+
+/* ---- StereoSGBM.compute ---- */
+/* Bytes of device workspace needed for a batch of B pairs processed concurrently. */
+int svb_sgbm_workspace_bytes(const svb_sgbm_params *raw, int H, int W, int channels, int B, size_t *bytes);
+/* left/right: u8 [B][H][pitch] (channels interleaved, 1 or 3), disp: int16 [B][H][disp_pitch_elems].
+ * ws may be NULL: the context then keeps a grow-only cached workspace of its own. */
+int svb_sgbm_compute(svb_context *ctx, const svb_sgbm_params *raw, const uint8_t *left, const uint8_t *right,
+                     int H, int W, int channels, size_t pitch_bytes, size_t image_stride_bytes, int B,
+                     int16_t *disp, size_t disp_pitch_elems, size_t disp_stride_elems, void *ws, size_t ws_bytes,
+                     void *stream);
+/* Stage taps for parity tests (single pair): cost volume C and aggregated volume S, both int16
+ * [H][width1][Dp]; disp_raw = selection output before median/speckle.  Any output may be NULL. */
+int svb_sgbm_debug_stages(svb_context *ctx, const svb_sgbm_params *raw, const uint8_t *left, const uint8_t *right,
+                          int H, int W, int channels, size_t pitch_bytes, int16_t *Cvol, int16_t *Svol,
+                          int16_t *disp_raw, void *stream);
+
+/* ---- post filters (also usable stand-alone, like cv2.medianBlur(.,3) / cv2.filterSpeckles) ---- */
+int svb_median3_s16(svb_context *ctx, const int16_t *src, int16_t *dst, int H, int W, size_t pitch_elems, int B,
+                    size_t stride_elems, void *stream);
+/* labels_ws: int32 workspace of at least 2*H*W elements per image (B images). In place on img. */
+int svb_filter_speckles_s16(svb_context *ctx, int16_t *img, int H, int W, size_t pitch_elems, int B,
+                            size_t stride_elems, int newVal, int maxSpeckleSize, int maxDiff, int32_t *labels_ws,
+                            size_t labels_ws_elems, void *stream);
+
+/* ---- rectification ---- */
+/* K[9], dist[ndist] (ndist in 0,4,5,8,12,14), R[9] (NULL = I), P33[9] = P[:3,:3] (NULL = K): HOST pointers
+ * (calibration-time scalars).  mapx/mapy: device f32 [H][W]. */
+int svb_init_undistort_rectify_map(svb_context *ctx, const double *K, const double *dist, int ndist,
+                                   const double *R, const double *P33, int W, int H, float *mapx, float *mapy,
+                                   void *stream);
+/* src: u8 [B][sH][spitch] with C in {1,3}; mapx/mapy f32 [dH][dW] shared by the batch;
+ * dst: u8 [B][dH][dpitch].  INTER_LINEAR, BORDER_CONSTANT(0): cv2's fixed-point tables. */
+int svb_remap_u8(svb_context *ctx, const uint8_t *src, int sH, int sW, int C, size_t spitch, size_t sstride,
+                 const float *mapx, const float *mapy, uint8_t *dst, int dH, int dW, size_t dpitch, size_t dstride,
+                 int B, void *stream);
+
+/* ---- 3-D ---- */
+/* dtype: 0=u8 1=s16 2=s32 3=f32 (raw value used, no /16 — as cv2).  Q: HOST double[16]. xyz: f32 [B][H][W][3].
+ * min_ws: device workspace of B doubles (only read/written when handle_missing). */
+int svb_reproject_to_3d(svb_context *ctx, const void *disp, int dtype, int H, int W, const double *Q,
+                        int handle_missing, float *xyz, int B, double *min_ws, void *stream);
+/* disp16: int16 [B][H][W] (x16, as compute returns); boxes: f32 [nboxes][4] xyxy; box_image: int32 [nboxes]
+ * (frame index of each box, NULL = all 0); out: f32 [nboxes].  scratch: f32, >= sum of clipped box areas
+ * (pass scratch_elems; the call fails with SVB_ERR_WORKSPACE if too small — bound: nboxes*max_box_area). */
+int svb_box_median_depth(svb_context *ctx, const int16_t *disp16, int H, int W, size_t stride_elems,
+                         const double *Q, int invalid16, const float *boxes, const int32_t *box_image, int nboxes,
+                         float *out, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SVB_H */

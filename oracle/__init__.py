@@ -104,6 +104,15 @@ def sgbm_stages(left, right, **kw):
     return raw, Cv, S
 
 
+def aggregate(Cvol, P1, P2, ndirs) -> np.ndarray:
+    """Saturated sum of the first `ndirs` path directions (order: left, up-left, up, up-right, right, ...)."""
+    Cvol = np.ascontiguousarray(Cvol, np.int16)
+    H, W1, D = Cvol.shape
+    S = np.empty_like(Cvol)
+    lib().svo_sgbm_aggregate_dirs(_p(Cvol), H, W1, D, int(P1), int(P2), int(ndirs), _p(S))
+    return S
+
+
 def median3(a) -> np.ndarray:
     a = np.ascontiguousarray(a, np.int16)
     out = np.empty_like(a)

@@ -257,13 +257,16 @@ static void aggregate_dir(const int16_t *Cvol, int16_t *S, int H, int W1, int D,
 }
 
 /* Aggregated volume S (sat int16) for mode 0 (5 paths) or 1 (8 paths). */
-int svo_sgbm_aggregate(const int16_t *Cvol, int H, int W1, int D, int P1, int P2, int mode, int16_t *S)
+int svo_sgbm_aggregate_dirs(const int16_t *Cvol, int H, int W1, int D, int P1, int P2, int ndirs, int16_t *S)
 {
     memset(S, 0, sizeof(int16_t) * (size_t)H * W1 * D);
     static const int dirs[8][2] = {{-1, 0}, {-1, -1}, {0, -1}, {1, -1}, {1, 0}, {1, 1}, {0, 1}, {-1, 1}};
-    int nd = mode == 1 ? 8 : 5;
-    for (int i = 0; i < nd; i++) aggregate_dir(Cvol, S, H, W1, D, dirs[i][0], dirs[i][1], P1, P2);
+    for (int i = 0; i < ndirs && i < 8; i++) aggregate_dir(Cvol, S, H, W1, D, dirs[i][0], dirs[i][1], P1, P2);
     return 0;
+}
+int svo_sgbm_aggregate(const int16_t *Cvol, int H, int W1, int D, int P1, int P2, int mode, int16_t *S)
+{
+    return svo_sgbm_aggregate_dirs(Cvol, H, W1, D, P1, P2, mode == 1 ? 8 : 5, S);
 }
 
 /* SURVEY.md §3.2.5 — WTA, uniqueness, subpixel, disp2 scatter, LR check; one image. */
@@ -283,11 +286,9 @@ void svo_sgbm_select(const int16_t *S, int H, int W, int W1, int D, const svo_pa
             for (int x = 0; x < W; x++) { d1[x] = (int16_t)INVALID; disp2[x] = INVALID; disp2cost[x] = SVO_MAX_COST; }
             for (int xi = W1 - 1; xi >= 0; xi--) {
                 const int16_t *Sp = S + (size_t)y * rowsz + (size_t)xi * D;
-                int minS = SVO_MAX_COST + 1, bestD = -1;
-                /* cv2 starts from minS = MAX_COST and uses strict <; a row of all-32767 keeps bestD=-1
-                 * there.  SIMD paths in 4.13 start at MAX_COST too; with all S==MAX_COST bestD stays -1.
-                 * (probe: see tests/golden, saturation cases) */
-                minS = SVO_MAX_COST; bestD = -1;
+                /* cv2 starts from minS = MAX_COST, bestDisp = -1 and uses strict <: a pixel whose costs are all
+                 * saturated keeps bestDisp = -1 (handled below; ends as INVALID). */
+                int minS = SVO_MAX_COST, bestD = -1;
                 for (int d = 0; d < D; d++)
                     if (Sp[d] < minS) { minS = Sp[d]; bestD = d; }
                 int d;

@@ -1,0 +1,343 @@
+"""cv2-compatible call surface for the dense stereo hot path.
+
+Drop-in for the cv2 names the reference's helpers use or would use:
+    StereoSGBM_create(...).compute(left, right)      (north_star; Q made at checkerboard_distance.py:49-51)
+    initUndistortRectifyMap / remap                  (checkerboard_distance.py:54-57, 71-72;
+                                                      calibrate_v4/distance.py:148-155; calibrate_v4/extrinsic.py:371-378)
+    reprojectImageTo3D, filterSpeckles, medianBlur(ksize=3, int16)
+    box_median_depth                                 (dense re-definition of ball_drop.py:89-160 + :225-259)
+
+NumPy in -> NumPy out (H2D/D2H inside).  torch CUDA tensor in -> torch CUDA tensor out, zero-copy on the current
+stream.  Every function runs hand-written sm_100a kernels through the C ABI (include/svb.h); there is no CPU path.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import SgbmParams, SgbmGeometry, check
+
+STEREO_SGBM_MODE_SGBM = 0
+STEREO_SGBM_MODE_HH = 1
+STEREO_SGBM_MODE_SGBM_3WAY = 2
+STEREO_SGBM_MODE_HH4 = 3
+INTER_LINEAR = 1
+BORDER_CONSTANT = 0
+CV_32FC1 = 5
+CV_16SC2 = 11
+
+_PARAM_NAMES = ("minDisparity", "numDisparities", "blockSize", "P1", "P2", "disp12MaxDiff", "preFilterCap",
+                "uniquenessRatio", "speckleWindowSize", "speckleRange", "mode")
+
+
+def _device_of(*xs) -> int:
+    for x in xs:
+        if isinstance(x, torch.Tensor):
+            if not x.is_cuda:
+                raise ValueError("torch tensors must live on a CUDA device (no CPU path)")
+            return x.device.index
+    if not torch.cuda.is_available():
+        raise _lib.SvbError("no CUDA device available — stereo_vision_b200 has no CPU fallback")
+    return torch.cuda.current_device()
+
+
+def _stream(dev: int) -> C.c_void_p:
+    return C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+
+
+def _as_dev(x, dev: int, dtype=None) -> torch.Tensor:
+    if isinstance(x, torch.Tensor):
+        t = x
+    else:
+        a = np.ascontiguousarray(x)
+        t = torch.from_numpy(a).to(f"cuda:{dev}", non_blocking=False)
+    if dtype is not None and t.dtype != dtype:
+        raise ValueError(f"expected dtype {dtype}, got {t.dtype}")
+    return t.contiguous()
+
+
+def _ptr(t) -> C.c_void_p:
+    return C.c_void_p(t.data_ptr()) if t is not None else C.c_void_p(0)
+
+
+_ws_cache: dict = {}
+
+
+def _workspace(dev: int, nbytes: int) -> torch.Tensor:
+    t = _ws_cache.get(dev)
+    if t is None or t.numel() < nbytes:
+        _ws_cache.pop(dev, None)
+        t = None
+        torch.cuda.synchronize(dev)
+        t = torch.empty(nbytes, dtype=torch.uint8, device=f"cuda:{dev}")
+        _ws_cache[dev] = t
+    return t
+
+
+def release_workspaces() -> None:
+    _ws_cache.clear()
+
+
+def _out(t: torch.Tensor, like):
+    return t if isinstance(like, torch.Tensor) else t.cpu().numpy()
+
+
+class StereoSGBM:
+    """Mirror of cv2.StereoSGBM: same 11 parameters, getters/setters and compute()."""
+
+    def __init__(self, minDisparity=0, numDisparities=16, blockSize=3, P1=0, P2=0, disp12MaxDiff=0, preFilterCap=0,
+                 uniquenessRatio=0, speckleWindowSize=0, speckleRange=0, mode=STEREO_SGBM_MODE_SGBM):
+        vals = (minDisparity, numDisparities, blockSize, P1, P2, disp12MaxDiff, preFilterCap, uniquenessRatio,
+                speckleWindowSize, speckleRange, mode)
+        self._p = {n: int(v) for n, v in zip(_PARAM_NAMES, vals)}
+
+    # ---- parameters ----
+    def _raw(self) -> SgbmParams:
+        return SgbmParams(*[self._p[n] for n in _PARAM_NAMES])
+
+    def effective_params(self) -> dict:
+        out = SgbmParams()
+        check(_lib.load().svb_sgbm_resolve_params(C.byref(self._raw()), C.byref(out)))
+        return {n: getattr(out, n) for n in _PARAM_NAMES}
+
+    def geometry(self, width: int, channels: int = 1) -> dict:
+        g = SgbmGeometry()
+        check(_lib.load().svb_sgbm_get_geometry(C.byref(self._raw()), int(width), int(channels), C.byref(g)))
+        return {n: getattr(g, n) for n, _ in SgbmGeometry._fields_}
+
+    # ---- compute ----
+    @staticmethod
+    def _check_pair(left, right, batched: bool):
+        ls, rs = tuple(left.shape), tuple(right.shape)
+        ld = left.dtype
+        if ls != rs or ld != right.dtype or ld not in (np.uint8, torch.uint8):
+            raise ValueError("left.size() == right.size() && left.type() == right.type() && left.depth() == CV_8U")
+        nd = len(ls) - (1 if batched else 0)
+        if nd == 2:
+            ch = 1
+        elif nd == 3 and ls[-1] in (1, 3):
+            ch = ls[-1]
+        else:
+            raise ValueError(f"images must be HxW or HxWx{{1,3}} uint8 (got shape {ls})")
+        return ch
+
+    def compute(self, left, right):
+        """left/right: HxW or HxWx3 uint8 (NumPy or torch CUDA).  Returns int16 HxW disparity * 16."""
+        self._check_pair(left, right, False)
+        dev = _device_of(left, right)
+        L = _as_dev(left, dev, torch.uint8)
+        R = _as_dev(right, dev, torch.uint8)
+        out = self._run(L[None], R[None], dev)[0]
+        return _out(out, left)
+
+    def compute_batch(self, left, right):
+        """Extension: [B,H,W] or [B,H,W,3] uint8 -> [B,H,W] int16.  All pairs are in flight concurrently."""
+        self._check_pair(left, right, True)
+        dev = _device_of(left, right)
+        out = self._run(_as_dev(left, dev, torch.uint8), _as_dev(right, dev, torch.uint8), dev)
+        return _out(out, left)
+
+    def _run(self, L: torch.Tensor, R: torch.Tensor, dev: int, out: torch.Tensor | None = None) -> torch.Tensor:
+        lib = _lib.load()
+        B, H, W = L.shape[0], L.shape[1], L.shape[2]
+        ch = 1 if L.dim() == 3 else L.shape[3]
+        raw = self._raw()
+        nb = C.c_size_t()
+        check(lib.svb_sgbm_workspace_bytes(C.byref(raw), H, W, ch, B, C.byref(nb)))
+        with torch.cuda.device(dev):
+            ws = _workspace(dev, nb.value)
+            if out is None:
+                out = torch.empty((B, H, W), dtype=torch.int16, device=L.device)
+            check(lib.svb_sgbm_compute(_lib.context(dev), C.byref(raw), _ptr(L), _ptr(R), H, W, ch, W * ch, H * W * ch, B,
+                                       _ptr(out), W, H * W, _ptr(ws), ws.numel(), _stream(dev)))
+        return out
+
+    def debug_stages(self, left, right):
+        """Stage taps for parity tests: (C [H,W1,Dp], S_pass1 [H,W1,Dp], disp_raw [H,W]) as NumPy."""
+        ch = self._check_pair(left, right, False)
+        dev = _device_of(left, right)
+        L = _as_dev(left, dev, torch.uint8)
+        R = _as_dev(right, dev, torch.uint8)
+        H, W = L.shape[0], L.shape[1]
+        g = self.geometry(W, ch)
+        Cv = torch.empty((H, g["width1"], g["Dp"]), dtype=torch.int16, device=L.device)
+        Sv = torch.empty_like(Cv)
+        raw_d = torch.empty((H, W), dtype=torch.int16, device=L.device)
+        with torch.cuda.device(dev):
+            check(_lib.load().svb_sgbm_debug_stages(_lib.context(dev), C.byref(self._raw()), _ptr(L), _ptr(R), H, W, ch,
+                                                    W * ch, _ptr(Cv), _ptr(Sv), _ptr(raw_d), _stream(dev)))
+        return Cv.cpu().numpy(), Sv.cpu().numpy(), raw_d.cpu().numpy()
+
+
+def _mk_accessors():
+    for n in _PARAM_NAMES:
+        cap = n[0].upper() + n[1:]
+
+        def getter(self, _n=n):
+            return self._p[_n]
+
+        def setter(self, v, _n=n):
+            self._p[_n] = int(v)
+
+        setattr(StereoSGBM, "get" + cap, getter)
+        setattr(StereoSGBM, "set" + cap, setter)
+
+
+_mk_accessors()
+
+
+def StereoSGBM_create(minDisparity=0, numDisparities=16, blockSize=3, P1=0, P2=0, disp12MaxDiff=0, preFilterCap=0,
+                      uniquenessRatio=0, speckleWindowSize=0, speckleRange=0, mode=STEREO_SGBM_MODE_SGBM) -> StereoSGBM:
+    return StereoSGBM(minDisparity, numDisparities, blockSize, P1, P2, disp12MaxDiff, preFilterCap, uniquenessRatio,
+                      speckleWindowSize, speckleRange, mode)
+
+
+# ---------------------------------------------------------------- rectification
+def initUndistortRectifyMap(cameraMatrix, distCoeffs, R, newCameraMatrix, size, m1type=CV_32FC1, device=None):
+    """cv2.initUndistortRectifyMap(K, dist, R, P, (W,H), CV_32FC1) -> (map1, map2) float32 HxW.
+    Returns NumPy maps unless `device` is given (then torch CUDA tensors that stay resident)."""
+    if m1type != CV_32FC1:
+        raise NotImplementedError("only m1type=CV_32FC1 (the only form the reference uses) is implemented")
+    W, H = int(size[0]), int(size[1])
+    K = np.ascontiguousarray(np.asarray(cameraMatrix, np.float64).reshape(3, 3))
+    dist = np.zeros(0) if distCoeffs is None else np.ascontiguousarray(np.asarray(distCoeffs, np.float64).ravel())
+    Rm = None if R is None else np.ascontiguousarray(np.asarray(R, np.float64).reshape(3, 3))
+    P33 = None
+    if newCameraMatrix is not None:
+        P = np.asarray(newCameraMatrix, np.float64)
+        if P.shape not in ((3, 3), (3, 4)):
+            raise ValueError("newCameraMatrix must be 3x3 or 3x4")
+        P33 = np.ascontiguousarray(P[:3, :3])
+    keep_dev = device is not None
+    dev = _device_of() if device is None else torch.device(device).index or 0
+    with torch.cuda.device(dev):
+        mx = torch.empty((H, W), dtype=torch.float32, device=f"cuda:{dev}")
+        my = torch.empty_like(mx)
+        check(_lib.load().svb_init_undistort_rectify_map(
+            _lib.context(dev), K.ctypes.data_as(C.c_void_p), dist.ctypes.data_as(C.c_void_p) if dist.size else None,
+            int(dist.size), Rm.ctypes.data_as(C.c_void_p) if Rm is not None else None,
+            P33.ctypes.data_as(C.c_void_p) if P33 is not None else None, W, H, _ptr(mx), _ptr(my), _stream(dev)))
+    if keep_dev:
+        return mx, my
+    return mx.cpu().numpy(), my.cpu().numpy()
+
+
+def remap(src, map1, map2, interpolation=INTER_LINEAR, dst=None, borderMode=BORDER_CONSTANT, borderValue=0):
+    """cv2.remap(src, map1, map2, cv2.INTER_LINEAR) for uint8 HxW / HxWx3 (or batched [B,H,W(,3)] tensors with
+    shared maps); float32 maps; BORDER_CONSTANT 0.  Bit-exact with cv2's fixed-point tables."""
+    if interpolation != INTER_LINEAR or borderMode != BORDER_CONSTANT or np.any(np.asarray(borderValue) != 0):
+        raise NotImplementedError("only INTER_LINEAR with BORDER_CONSTANT(0) (the reference's call) is implemented")
+    if src.dtype not in (np.uint8, torch.uint8):
+        raise ValueError("remap: only uint8 images are supported")
+    dev = _device_of(src, map1, map2)
+    S = _as_dev(src, dev, torch.uint8)
+    mx = _as_dev(map1, dev, torch.float32)
+    my = _as_dev(map2, dev, torch.float32)
+    if mx.shape != my.shape or mx.dim() != 2:
+        raise ValueError("map1/map2 must be float32 HxW arrays of equal shape")
+    dH, dW = mx.shape
+    batched = isinstance(src, torch.Tensor) and (S.dim() == 4 or (S.dim() == 3 and S.shape[-1] not in (1, 3)))
+    Sb = S if batched else S[None]
+    ch = 1 if Sb.dim() == 3 else Sb.shape[3]
+    if ch not in (1, 3):
+        raise ValueError("remap: 1- or 3-channel images only")
+    B, sH, sW = Sb.shape[0], Sb.shape[1], Sb.shape[2]
+    shape = (B, dH, dW) if Sb.dim() == 3 else (B, dH, dW, ch)
+    with torch.cuda.device(dev):
+        out = torch.empty(shape, dtype=torch.uint8, device=S.device)
+        check(_lib.load().svb_remap_u8(_lib.context(dev), _ptr(Sb), sH, sW, ch, sW * ch, sH * sW * ch, _ptr(mx), _ptr(my),
+                                       _ptr(out), dH, dW, dW * ch, dH * dW * ch, B, _stream(dev)))
+    out = out if batched else out[0]
+    return _out(out, src)
+
+
+# ---------------------------------------------------------------- post filters
+def medianBlur(src, ksize):
+    """cv2.medianBlur(disp_int16, 3) (BORDER_REPLICATE) — the filter compute() applies internally."""
+    if ksize != 3 or src.dtype not in (np.int16, torch.int16) or src.ndim != 2:
+        raise NotImplementedError("only ksize=3 on int16 HxW maps is implemented")
+    dev = _device_of(src)
+    s = _as_dev(src, dev, torch.int16)
+    H, W = s.shape
+    with torch.cuda.device(dev):
+        out = torch.empty_like(s)
+        check(_lib.load().svb_median3_s16(_lib.context(dev), _ptr(s), _ptr(out), H, W, W, 1, H * W, _stream(dev)))
+    return _out(out, src)
+
+
+def filterSpeckles(img, newVal, maxSpeckleSize, maxDiff, buf=None):
+    """cv2.filterSpeckles(img, newVal, maxSpeckleSize, maxDiff): in place on int16 HxW; returns (img, None)."""
+    if img.dtype not in (np.int16, torch.int16) or img.ndim != 2:
+        raise ValueError("filterSpeckles: int16 HxW image required")
+    dev = _device_of(img)
+    t = _as_dev(img, dev, torch.int16)
+    if not isinstance(img, torch.Tensor):
+        t = t.clone()
+    H, W = t.shape
+    with torch.cuda.device(dev):
+        labels = torch.empty(2 * H * W, dtype=torch.int32, device=t.device)
+        check(_lib.load().svb_filter_speckles_s16(_lib.context(dev), _ptr(t), H, W, W, 1, H * W, int(newVal),
+                                                  int(maxSpeckleSize), int(maxDiff), _ptr(labels), labels.numel(),
+                                                  _stream(dev)))
+    if isinstance(img, torch.Tensor):
+        if t.data_ptr() != img.data_ptr():
+            img.copy_(t)
+        return img, None
+    img[...] = t.cpu().numpy()
+    return img, None
+
+
+# ---------------------------------------------------------------- 3-D
+_DT = {torch.uint8: 0, torch.int16: 1, torch.int32: 2, torch.float32: 3}
+
+
+def reprojectImageTo3D(disparity, Q, _3dImage=None, handleMissingValues=False, ddepth=-1):
+    """cv2.reprojectImageTo3D(disp, Q, handleMissingValues) -> float32 HxWx3 (raw disparity values, no /16)."""
+    if ddepth not in (-1, CV_32FC1):
+        raise NotImplementedError("only float32 output (ddepth=-1) is implemented")
+    dev = _device_of(disparity)
+    d = _as_dev(disparity, dev)
+    if d.dtype not in _DT or d.dim() not in (2, 3):
+        raise ValueError("disparity must be CV_8UC1, CV_16SC1, CV_32SC1 or CV_32FC1 (HxW)")
+    Qh = np.ascontiguousarray(np.asarray(Q, np.float64))
+    if Qh.shape != (4, 4):
+        raise ValueError("Q must be 4x4")
+    db = d if d.dim() == 3 else d[None]
+    B, H, W = db.shape
+    with torch.cuda.device(dev):
+        out = torch.empty((B, H, W, 3), dtype=torch.float32, device=d.device)
+        mins = torch.empty(B, dtype=torch.float64, device=d.device) if handleMissingValues else None
+        check(_lib.load().svb_reproject_to_3d(_lib.context(dev), _ptr(db), _DT[d.dtype], H, W,
+                                              Qh.ctypes.data_as(C.c_void_p), int(bool(handleMissingValues)), _ptr(out),
+                                              B, _ptr(mins), _stream(dev)))
+    out = out if d.dim() == 3 else out[0]
+    return _out(out, disparity)
+
+
+def box_median_depth(disp16, Q, boxes, minDisparity=0, box_image=None):
+    """Fused reprojection + per-box median depth.  disp16: int16 HxW (or [B,H,W]) as compute() returns;
+    boxes: N x 4 float32 xyxy (ultralytics boxes.data[:, :4]) in left-image pixels; box_image: frame index per box
+    for batched maps.  Returns float32 N: median Z over valid pixels (NaN when none).  SURVEY.md §8a row a10."""
+    dev = _device_of(disp16, boxes)
+    d = _as_dev(disp16, dev, torch.int16)
+    bx = _as_dev(np.asarray(boxes, np.float32).reshape(-1, 4) if not isinstance(boxes, torch.Tensor) else boxes, dev,
+                 torch.float32).reshape(-1, 4)
+    Qh = np.ascontiguousarray(np.asarray(Q, np.float64))
+    if Qh.shape != (4, 4):
+        raise ValueError("Q must be 4x4")
+    db = d if d.dim() == 3 else d[None]
+    _, H, W = db.shape
+    bi = None
+    if box_image is not None:
+        bi = _as_dev(np.asarray(box_image, np.int32) if not isinstance(box_image, torch.Tensor) else box_image, dev,
+                     torch.int32)
+    n = bx.shape[0]
+    with torch.cuda.device(dev):
+        out = torch.empty(n, dtype=torch.float32, device=d.device)
+        check(_lib.load().svb_box_median_depth(_lib.context(dev), _ptr(db), H, W, H * W, Qh.ctypes.data_as(C.c_void_p),
+                                               (int(minDisparity) - 1) * 16, _ptr(bx), _ptr(bi), n, _ptr(out),
+                                               _stream(dev)))
+    return out if isinstance(disp16, torch.Tensor) else out.cpu().numpy()

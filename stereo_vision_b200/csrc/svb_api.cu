@@ -1,0 +1,253 @@
+// svb_api.cu — context, parameter resolution, workspace plan and the StereoSGBM.compute entry points.
+#include "svb_common.cuh"
+#include <algorithm>
+
+static thread_local char g_err[512] = "";
+
+void svb_set_error(const char *fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof g_err, fmt, ap);
+    va_end(ap);
+}
+
+extern "C" const char *svb_last_error(void) { return g_err; }
+extern "C" const char *svb_version(void) { return "svb 0.1 (sm_100a)"; }
+
+extern "C" int svb_create(int device_id, svb_context **out)
+{
+    SVB_REQUIRE(out, SVB_ERR_INVALID, "svb_create: null out pointer");
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0) {
+        svb_set_error("svb_create: no CUDA device available (%s) — this engine has no CPU fallback",
+                      e == cudaSuccess ? "device count 0" : cudaGetErrorString(e));
+        return SVB_ERR_CUDA;
+    }
+    SVB_REQUIRE(device_id >= 0 && device_id < n, SVB_ERR_INVALID, "svb_create: device %d out of range (%d devices)",
+                device_id, n);
+    SVB_CUDA_CHECK(cudaSetDevice(device_id));
+    cudaDeviceProp prop;
+    SVB_CUDA_CHECK(cudaGetDeviceProperties(&prop, device_id));
+    SVB_REQUIRE(prop.major >= 10, SVB_ERR_UNSUPPORTED, "svb_create: device %s is sm_%d%d; libsvb is built for sm_100a only",
+                prop.name, prop.major, prop.minor);
+    svb_context *c = new svb_context();
+    c->device = device_id;
+    c->num_sms = prop.multiProcessorCount;
+    c->ws = nullptr;
+    c->ws_bytes = 0;
+    c->tickets = nullptr;
+    e = cudaMalloc(&c->tickets, 16 * sizeof(unsigned));
+    if (e != cudaSuccess) {
+        delete c;
+        svb_set_error("svb_create: cudaMalloc failed: %s", cudaGetErrorString(e));
+        return SVB_ERR_CUDA;
+    }
+    *out = c;
+    return SVB_OK;
+}
+
+extern "C" int svb_destroy(svb_context *ctx)
+{
+    if (!ctx) return SVB_OK;
+    cudaSetDevice(ctx->device);
+    if (ctx->ws) cudaFree(ctx->ws);
+    if (ctx->tickets) cudaFree(ctx->tickets);
+    delete ctx;
+    return SVB_OK;
+}
+
+// SURVEY.md §3.2.1
+extern "C" int svb_sgbm_resolve_params(const svb_sgbm_params *raw, svb_sgbm_params *e)
+{
+    SVB_REQUIRE(raw && e, SVB_ERR_INVALID, "resolve_params: null argument");
+    *e = *raw;
+    e->blockSize = raw->blockSize > 0 ? raw->blockSize : 5;
+    e->P1 = raw->P1 > 0 ? raw->P1 : 2;
+    e->P2 = std::max(raw->P2 > 0 ? raw->P2 : 5, e->P1 + 1);
+    e->preFilterCap = std::max(raw->preFilterCap, 15) | 1;
+    e->uniquenessRatio = raw->uniquenessRatio >= 0 ? raw->uniquenessRatio : 10;
+    e->disp12MaxDiff = raw->disp12MaxDiff > 0 ? raw->disp12MaxDiff : 1;
+    return SVB_OK;
+}
+
+static int next_pow2(int v)
+{
+    int p = 1;
+    while (p < v) p <<= 1;
+    return p;
+}
+
+int svb_make_plan(const svb_sgbm_params *raw, int H, int W, int ch, SgbmPlan *pl)
+{
+    SVB_REQUIRE(raw && pl, SVB_ERR_INVALID, "sgbm: null argument");
+    memset(pl, 0, sizeof *pl);
+    svb_sgbm_resolve_params(raw, &pl->p);
+    const svb_sgbm_params &p = pl->p;
+    SVB_REQUIRE(ch == 1 || ch == 3, SVB_ERR_INVALID, "sgbm: images must be CV_8UC1 or CV_8UC3 (channels=%d)", ch);
+    SVB_REQUIRE(H > 0 && W > 0, SVB_ERR_INVALID, "sgbm: bad image size %dx%d", W, H);
+    SVB_REQUIRE(p.numDisparities > 0, SVB_ERR_INVALID, "sgbm: numDisparities must be positive (got %d)", p.numDisparities);
+    SVB_REQUIRE(p.mode == 0 || p.mode == 1, SVB_ERR_UNSUPPORTED,
+                "sgbm: mode %d not implemented (MODE_SGBM=0 and MODE_HH=1 only)", p.mode);
+    pl->H = H; pl->W = W; pl->ch = ch;
+    const int minD = p.minDisparity, D = p.numDisparities, maxD = minD + D;
+    pl->D = D;
+    pl->minX1 = std::max(maxD, 0);
+    pl->maxX1 = W + std::min(minD, 0);
+    pl->W1 = pl->maxX1 - pl->minX1;
+    pl->R = p.blockSize / 2;
+    // cv2 4.13: "width - (minDisparity+numDisparities) > blockSize/2" else error -2
+    SVB_REQUIRE(W - maxD > pl->R && pl->W1 > 0, SVB_ERR_INVALID,
+                "sgbm: image width %d is too small for minDisparity+numDisparities=%d and blockSize=%d", W, maxD,
+                p.blockSize);
+    SVB_REQUIRE(pl->R <= 5, SVB_ERR_UNSUPPORTED, "sgbm: blockSize %d > 11 is outside this engine's contract", p.blockSize);
+    SVB_REQUIRE(D <= 512, SVB_ERR_UNSUPPORTED, "sgbm: numDisparities %d > 512 is outside this engine's contract", D);
+    SVB_REQUIRE(W <= 65535 && H <= 65535, SVB_ERR_UNSUPPORTED, "sgbm: image larger than 65535 px");
+    pl->ftzero = p.preFilterCap;
+    pl->invalid16 = (minD - 1) * 16;
+    pl->nplanes = 2 * ch;
+    const int bs = 2 * pl->R + 1;
+    pl->max_cost = bs * bs * ch * (2 * pl->ftzero + 63);
+    SVB_REQUIRE(pl->max_cost + p.P2 <= 32767 && p.P1 + p.P2 <= 32767, SVB_ERR_UNSUPPORTED,
+                "sgbm: blockSize^2*channels*(2*preFilterCap+63)+P2 = %d exceeds int16 (cv2's cost type overflows too)",
+                pl->max_cost + p.P2);
+    pl->safe = (pl->max_cost + p.P2 <= 8191);
+    if (D <= 256) {
+        pl->E = 8;
+        pl->G = std::max(2, next_pow2((D + 7) / 8));
+    } else {
+        pl->E = 16;
+        pl->G = 32;
+    }
+    pl->Dp = pl->E * pl->G;
+    pl->NG = 16;
+    pl->nbands = (H + pl->NG - 1) / pl->NG;
+    pl->Wr = (int)svb_align_up((size_t)W + pl->Dp + 8, 8);
+    size_t off = 0;
+    auto take = [&](size_t bytes) { size_t o = off; off = svb_align_up(off + std::max<size_t>(bytes, 16), 256); return o; };
+    const size_t vol = (size_t)H * pl->W1 * pl->Dp * 2;
+    pl->off_lplanes = take((size_t)H * pl->nplanes * pl->W1 * 16);
+    pl->off_rplanes = take((size_t)H * pl->nplanes * 8 * pl->Wr * 2);
+    pl->off_C = take(vol);
+    pl->off_S = take(vol);
+    pl->off_edge = take((size_t)std::max(pl->nbands - 1, 1) * pl->W1 * 3 * pl->Dp * 2);
+    pl->off_prog = take(2 * sizeof(unsigned) * pl->nbands);
+    pl->off_dpre = take((size_t)H * W * 2);
+    pl->off_key = take((size_t)H * W * 4);
+    pl->off_dtmp = take((size_t)H * W * 2);
+    pl->off_labels = take((size_t)H * W * 8);
+    pl->per_frame_bytes = svb_align_up(off, 256);
+    return SVB_OK;
+}
+
+extern "C" int svb_sgbm_get_geometry(const svb_sgbm_params *raw, int W, int channels, svb_sgbm_geometry *g)
+{
+    SVB_REQUIRE(g, SVB_ERR_INVALID, "get_geometry: null argument");
+    SgbmPlan pl;
+    int rc = svb_make_plan(raw, 16, W, channels, &pl);
+    if (rc) return rc;
+    g->minX1 = pl.minX1; g->maxX1 = pl.maxX1; g->width1 = pl.W1; g->D = pl.D; g->Dp = pl.Dp;
+    g->invalid16 = pl.invalid16; g->max_cost = pl.max_cost; g->safe_packed = pl.safe;
+    return SVB_OK;
+}
+
+extern "C" int svb_sgbm_workspace_bytes(const svb_sgbm_params *raw, int H, int W, int channels, int B, size_t *bytes)
+{
+    SVB_REQUIRE(bytes && B > 0, SVB_ERR_INVALID, "workspace_bytes: bad argument");
+    SgbmPlan pl;
+    int rc = svb_make_plan(raw, H, W, channels, &pl);
+    if (rc) return rc;
+    *bytes = pl.per_frame_bytes * (size_t)B;
+    return SVB_OK;
+}
+
+static int get_workspace(svb_context *ctx, size_t need, void *user_ws, size_t user_bytes, char **out)
+{
+    if (user_ws) {
+        SVB_REQUIRE(user_bytes >= need, SVB_ERR_WORKSPACE, "sgbm: workspace too small (%zu < %zu bytes)", user_bytes, need);
+        SVB_REQUIRE(((uintptr_t)user_ws & 255) == 0, SVB_ERR_INVALID, "sgbm: workspace must be 256-byte aligned");
+        *out = (char *)user_ws;
+        return SVB_OK;
+    }
+    if (ctx->ws_bytes < need) {
+        SVB_CUDA_CHECK(cudaDeviceSynchronize());
+        if (ctx->ws) cudaFree(ctx->ws);
+        ctx->ws = nullptr;
+        ctx->ws_bytes = 0;
+        SVB_CUDA_CHECK(cudaMalloc(&ctx->ws, need));
+        ctx->ws_bytes = need;
+    }
+    *out = (char *)ctx->ws;
+    return SVB_OK;
+}
+
+static int run_front(svb_context *ctx, const SgbmPlan &pl, const uint8_t *left, const uint8_t *right, size_t pitch,
+                     size_t istride, int B, char *ws, cudaStream_t st)
+{
+    int rc;
+    if ((rc = svb_launch_planes(pl, left, right, pitch, istride, ws, pl.per_frame_bytes, B, st))) return rc;
+    if ((rc = svb_launch_cost(pl, ws, pl.per_frame_bytes, B, st))) return rc;
+    return SVB_OK;
+}
+
+extern "C" int svb_sgbm_compute(svb_context *ctx, const svb_sgbm_params *raw, const uint8_t *left, const uint8_t *right,
+                                int H, int W, int channels, size_t pitch_bytes, size_t image_stride_bytes, int B,
+                                int16_t *disp, size_t disp_pitch_elems, size_t disp_stride_elems, void *ws_user,
+                                size_t ws_bytes, void *stream)
+{
+    SVB_REQUIRE(ctx && left && right && disp, SVB_ERR_INVALID, "sgbm_compute: null argument");
+    SVB_REQUIRE(B > 0, SVB_ERR_INVALID, "sgbm_compute: batch must be positive");
+    SgbmPlan pl;
+    int rc = svb_make_plan(raw, H, W, channels, &pl);
+    if (rc) return rc;
+    SVB_REQUIRE(pitch_bytes >= (size_t)W * channels && disp_pitch_elems >= (size_t)W, SVB_ERR_INVALID,
+                "sgbm_compute: pitch smaller than a row");
+    SVB_CUDA_CHECK(cudaSetDevice(ctx->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    char *ws;
+    if ((rc = get_workspace(ctx, pl.per_frame_bytes * (size_t)B, ws_user, ws_bytes, &ws))) return rc;
+    if ((rc = run_front(ctx, pl, left, right, pitch_bytes, image_stride_bytes, B, ws, st))) return rc;
+    if ((rc = svb_launch_aggregate(ctx, pl, ws, pl.per_frame_bytes, B, st))) return rc;
+    if ((rc = svb_launch_lrcheck(pl, ws, pl.per_frame_bytes, B, st))) return rc;
+    if ((rc = svb_launch_median3((const int16_t *)(ws + pl.off_dtmp), disp, H, W, W, pl.per_frame_bytes / 2,
+                                 disp_pitch_elems, disp_stride_elems, B, st)))
+        return rc;
+    if (pl.p.speckleWindowSize > 0)
+        if ((rc = svb_launch_speckle(disp, H, W, disp_pitch_elems, disp_stride_elems, B, pl.invalid16,
+                                     pl.p.speckleWindowSize, 16 * pl.p.speckleRange, (int32_t *)(ws + pl.off_labels),
+                                     pl.per_frame_bytes / 4, st)))
+            return rc;
+    return SVB_OK;
+}
+
+extern "C" int svb_sgbm_debug_stages(svb_context *ctx, const svb_sgbm_params *raw, const uint8_t *left,
+                                     const uint8_t *right, int H, int W, int channels, size_t pitch_bytes, int16_t *Cvol,
+                                     int16_t *Svol, int16_t *disp_raw, void *stream)
+{
+    SVB_REQUIRE(ctx && left && right, SVB_ERR_INVALID, "sgbm_debug_stages: null argument");
+    SgbmPlan pl;
+    int rc = svb_make_plan(raw, H, W, channels, &pl);
+    if (rc) return rc;
+    SVB_CUDA_CHECK(cudaSetDevice(ctx->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    char *ws;
+    if ((rc = get_workspace(ctx, pl.per_frame_bytes, nullptr, 0, &ws))) return rc;
+    if ((rc = run_front(ctx, pl, left, right, pitch_bytes, 0, 1, ws, st))) return rc;
+    const size_t vol = (size_t)H * pl.W1 * pl.Dp * 2;
+    if (Cvol) SVB_CUDA_CHECK(cudaMemcpyAsync(Cvol, ws + pl.off_C, vol, cudaMemcpyDeviceToDevice, st));
+    if (Svol || disp_raw) {
+        if (Svol) {
+            // S after pass 1 only is what the volume holds; run pass 1 + a selection-free copy for mode 0/1:
+            // for the tap we want the FINAL S, which pass 2 keeps in registers — so tap pass-1 S here and
+            // let the test add the remaining directions' contribution through disp_raw parity instead.
+        }
+        if ((rc = svb_launch_aggregate(ctx, pl, ws, pl.per_frame_bytes, 1, st))) return rc;
+        if (Svol) SVB_CUDA_CHECK(cudaMemcpyAsync(Svol, ws + pl.off_S, vol, cudaMemcpyDeviceToDevice, st));
+        if (disp_raw) {
+            if ((rc = svb_launch_lrcheck(pl, ws, pl.per_frame_bytes, 1, st))) return rc;
+            SVB_CUDA_CHECK(cudaMemcpyAsync(disp_raw, ws + pl.off_dtmp, (size_t)H * W * 2, cudaMemcpyDeviceToDevice, st));
+        }
+    }
+    return SVB_OK;
+}

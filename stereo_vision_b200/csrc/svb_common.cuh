@@ -1,0 +1,76 @@
+// svb_common.cuh — shared host/device helpers for libsvb (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdarg.h>
+#include <string.h>
+
+#include "../../include/svb.h"
+
+#if defined(__CUDA_ARCH__) && (__CUDA_ARCH__ < 1000)
+#error "libsvb is written for sm_100a (B200) only"
+#endif
+
+void svb_set_error(const char *fmt, ...);
+
+#define SVB_CUDA_CHECK(expr)                                                                   \
+    do {                                                                                       \
+        cudaError_t _e = (expr);                                                               \
+        if (_e != cudaSuccess) {                                                               \
+            svb_set_error("CUDA error %s at %s:%d: %s", cudaGetErrorName(_e), __FILE__, __LINE__, \
+                          cudaGetErrorString(_e));                                             \
+            return SVB_ERR_CUDA;                                                               \
+        }                                                                                      \
+    } while (0)
+
+#define SVB_REQUIRE(cond, code, ...)      \
+    do {                                  \
+        if (!(cond)) {                    \
+            svb_set_error(__VA_ARGS__);   \
+            return (code);                \
+        }                                 \
+    } while (0)
+
+struct svb_context {
+    int device;
+    int num_sms;
+    void *ws;          // grow-only cached workspace
+    size_t ws_bytes;
+    unsigned int *tickets;  // device counters for the sweep scheduler
+};
+
+// ---- resolved SGBM plan (host) ----
+struct SgbmPlan {
+    svb_sgbm_params p;   // effective parameters
+    int H, W, ch;
+    int minX1, maxX1, W1, D, Dp, E, G;  // E elems/lane, G lanes/group; Dp = E*G
+    int R;               // block radius
+    int ftzero;
+    int invalid16;
+    int max_cost;
+    int safe;            // packed S accumulation cannot overflow
+    int nplanes;
+    // sweep geometry
+    int NG;              // row-groups per CTA (rows per band)
+    int nbands;
+    // workspace layout (bytes, per frame)
+    size_t off_lplanes, off_rplanes, off_C, off_S, off_edge, off_prog, off_dpre, off_key, off_dtmp, off_labels;
+    size_t per_frame_bytes;
+    int Wr;              // right-plane row length (elements) incl. padding
+};
+
+int svb_make_plan(const svb_sgbm_params *raw, int H, int W, int ch, SgbmPlan *plan);
+
+static inline size_t svb_align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+// kernels' host launchers (defined in the .cu files)
+int svb_launch_planes(const SgbmPlan &pl, const uint8_t *left, const uint8_t *right, size_t pitch, size_t istride,
+                      char *ws, size_t ws_stride, int B, cudaStream_t st);
+int svb_launch_cost(const SgbmPlan &pl, char *ws, size_t ws_stride, int B, cudaStream_t st);
+int svb_launch_aggregate(svb_context *ctx, const SgbmPlan &pl, char *ws, size_t ws_stride, int B, cudaStream_t st);
+int svb_launch_lrcheck(const SgbmPlan &pl, char *ws, size_t ws_stride, int B, cudaStream_t st);
+int svb_launch_median3(const int16_t *src, int16_t *dst, int H, int W, size_t spitch, size_t sstride, size_t dpitch,
+                       size_t dstride, int B, cudaStream_t st);
+int svb_launch_speckle(int16_t *img, int H, int W, size_t pitch, size_t stride, int B, int newVal, int maxSize,
+                       int maxDiff, int32_t *labels, size_t lstride, cudaStream_t st);

@@ -1,0 +1,110 @@
+"""GPU parity: StereoSGBM.compute through the C ABI vs the CPU oracle and the cv2 golden vectors (bit-exact)."""
+import hashlib
+
+import numpy as np
+import pytest
+
+import cases
+import oracle
+from stereo_vision_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+
+def _sha(a):
+    return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+
+
+def test_cost_volume_and_pass1_match_oracle(sv):
+    for (H, W, D, bs, ch, minD, kind) in [(40, 150, 64, 5, 1, 0, "smooth"), (37, 120, 24, 3, 3, -4, "noise"),
+                                           (33, 100, 16, 11, 1, 4, "binary"), (36, 140, 48, 7, 1, 0, "smooth")]:
+        L, R = synth.stereo_pair(H, W, D, seed=3, kind=kind, channels=ch)
+        kw = dict(minDisparity=minD, numDisparities=D, blockSize=bs, P1=8 * ch * bs * bs, P2=32 * ch * bs * bs,
+                  preFilterCap=63, uniquenessRatio=10, mode=1)
+        raw_o, C_o, S_o = oracle.sgbm_stages(L, R, **kw)
+        C_g, S_g, raw_g = sv.StereoSGBM_create(**kw).debug_stages(L, R)
+        assert np.array_equal(C_g[:, :, :D], C_o), f"cost volume mismatch {H}x{W} D={D} bs={bs}"
+        r = oracle.resolve(**kw)
+        S4 = oracle.aggregate(C_o, r["P1"], r["P2"], 4)
+        assert np.array_equal(S_g[:, :, :D], S4), f"pass-1 S mismatch {H}x{W} D={D}"
+        assert np.array_equal(raw_g, raw_o), f"pre-median disparity mismatch {H}x{W} D={D}"
+
+
+def test_small_sweep_matches_cv2_golden_and_oracle(sv, golden):
+    bad = []
+    for i, c in enumerate(cases.sgbm_small_cases()):
+        L, R = cases.sgbm_inputs(c)
+        got = sv.StereoSGBM_create(**c["kw"]).compute(L, R)
+        assert got.dtype == np.int16 and got.shape == L.shape[:2]
+        if not np.array_equal(got, golden[f"sgbm_{i}"]):
+            bad.append((i, c, int((got != golden[f"sgbm_{i}"]).sum())))
+    assert not bad, f"{len(bad)} of 96 cases differ from cv2 golden: {bad[:3]}"
+
+
+@pytest.mark.parametrize("name", ["c1", "c2", "c3", "c3_sgbm"])
+def test_full_size_matches_cv2_golden_hash(sv, golden_full, name):
+    L, R, kw = cases.full_inputs(name)
+    g = golden_full["full"][name]
+    assert [_sha(L), _sha(R)] == g["in_sha256"], "synthetic inputs are not reproducible on this host"
+    got = sv.StereoSGBM_create(**kw).compute(L, R)
+    if _sha(got) != g["sha256"]:
+        ref = oracle.sgbm_compute(L, R, **kw)
+        raise AssertionError(f"{name}: differs from cv2 golden; vs oracle: {(got != ref).sum()} px differ")
+
+
+def test_full_size_c5_4k(sv, golden_full):
+    L, R, kw = cases.full_inputs("c5")
+    got = sv.StereoSGBM_create(**kw).compute(L, R)
+    assert _sha(got) == golden_full["full"]["c5"]["sha256"]
+
+
+def test_batch_equals_single_and_torch_zero_copy(sv):
+    import torch
+    D, H, W = 64, 96, 320
+    kw = synth.sgbm_kwargs(D, 5, 1)
+    pairs = [synth.stereo_pair(H, W, D, seed=1000 + i) for i in range(5)]
+    Lb = torch.from_numpy(np.stack([p[0] for p in pairs])).cuda()
+    Rb = torch.from_numpy(np.stack([p[1] for p in pairs])).cuda()
+    m = sv.StereoSGBM_create(**kw)
+    out = m.compute_batch(Lb, Rb)
+    assert out.is_cuda and out.dtype == torch.int16
+    for i, (L, R) in enumerate(pairs):
+        assert np.array_equal(out[i].cpu().numpy(), oracle.sgbm_compute(L, R, **kw))
+        assert np.array_equal(m.compute(L, R), out[i].cpu().numpy())
+
+
+def test_properties_at_full_size(sv):
+    """Size-independent properties at 1080p/D=256: determinism, invalid left band, value range."""
+    L, R, kw = cases.full_inputs("c3")
+    m = sv.StereoSGBM_create(**kw)
+    a = m.compute(L, R)
+    b = m.compute(L, R)
+    assert np.array_equal(a, b)
+    D = kw["numDisparities"]
+    assert (a[:, :D] == -16).all()
+    v = a[a != -16]
+    assert v.min() >= 0 and v.max() <= (D - 1) * 16
+    # the synthetic field is recovered on most valid pixels
+    d_true = synth.disparity_field(L.shape[0], L.shape[1], D)
+    ok = (np.abs(a / 16.0 - d_true) <= 1)[a != -16].mean()
+    assert ok > 0.95
+
+
+def test_error_behaviour(sv):
+    m = sv.StereoSGBM_create(numDisparities=64, blockSize=5)
+    z = np.zeros((32, 128), np.uint8)
+    with pytest.raises(ValueError):
+        m.compute(z, np.zeros((32, 127), np.uint8))
+    with pytest.raises(ValueError):
+        m.compute(z.astype(np.float32), z.astype(np.float32))
+    with pytest.raises(ValueError):
+        m.compute(z[:, :60], z[:, :60])          # too narrow (cv2.error -2)
+    with pytest.raises(NotImplementedError):
+        sv.StereoSGBM_create(numDisparities=16, mode=2).compute(z, z)
+    with pytest.raises(ValueError):
+        sv.StereoSGBM_create(numDisparities=0).compute(z, z)
+    # non-contiguous views are accepted
+    big = np.random.default_rng(0).integers(0, 255, (64, 256), dtype=np.uint8)
+    v = big[::2, ::1]
+    assert np.array_equal(m.compute(v, v), oracle.sgbm_compute(np.ascontiguousarray(v), np.ascontiguousarray(v),
+                                                                numDisparities=64, blockSize=5))
