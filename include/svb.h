@@ -75,11 +75,18 @@ int svb_sgbm_compute(svb_context *ctx, const svb_sgbm_params *raw, const uint8_t
                      int H, int W, int channels, size_t pitch_bytes, size_t image_stride_bytes, int B,
                      int16_t *disp, size_t disp_pitch_elems, size_t disp_stride_elems, void *ws, size_t ws_bytes,
                      void *stream);
-/* Stage taps for parity tests (single pair): cost volume C and aggregated volume S, both int16
- * [H][width1][Dp]; disp_raw = selection output before median/speckle.  Any output may be NULL. */
+/* Stage taps for parity tests (single pair): cost volume C and the pass-1 aggregate S (sum of the four
+ * forward paths; the final S only ever exists in registers), both int16 [H][width1][Dp]; disp_raw = selection
+ * + LR-check output before median/speckle.  Any output may be NULL. */
 int svb_sgbm_debug_stages(svb_context *ctx, const svb_sgbm_params *raw, const uint8_t *left, const uint8_t *right,
                           int H, int W, int channels, size_t pitch_bytes, int16_t *Cvol, int16_t *Svol,
                           int16_t *disp_raw, void *stream);
+
+/* Per-stage device times (ms) of the last svb_sgbm_compute on this context (CUDA events on the caller's stream):
+ * ms[0..5] = planes, cost volume, aggregation pass 1, aggregation pass 2 + selection, LR check + median, speckle.
+ * Enable with svb_set_timing(ctx,1); svb_sgbm_last_stage_ms blocks until that call has finished. */
+int svb_set_timing(svb_context *ctx, int enable);
+int svb_sgbm_last_stage_ms(svb_context *ctx, float *ms, int n);
 
 /* ---- post filters (also usable stand-alone, like cv2.medianBlur(.,3) / cv2.filterSpeckles) ---- */
 int svb_median3_s16(svb_context *ctx, const int16_t *src, int16_t *dst, int H, int W, size_t pitch_elems, int B,
@@ -107,8 +114,8 @@ int svb_remap_u8(svb_context *ctx, const uint8_t *src, int sH, int sW, int C, si
 int svb_reproject_to_3d(svb_context *ctx, const void *disp, int dtype, int H, int W, const double *Q,
                         int handle_missing, float *xyz, int B, double *min_ws, void *stream);
 /* disp16: int16 [B][H][W] (x16, as compute returns); boxes: f32 [nboxes][4] xyxy; box_image: int32 [nboxes]
- * (frame index of each box, NULL = all 0); out: f32 [nboxes].  scratch: f32, >= sum of clipped box areas
- * (pass scratch_elems; the call fails with SVB_ERR_WORKSPACE if too small — bound: nboxes*max_box_area). */
+ * (frame index of each box, NULL = all 0); out: f32 [nboxes]: median Z over valid pixels, NaN if none.
+ */
 int svb_box_median_depth(svb_context *ctx, const int16_t *disp16, int H, int W, size_t stride_elems,
                          const double *Q, int invalid16, const float *boxes, const int32_t *box_image, int nboxes,
                          float *out, void *stream);

@@ -341,3 +341,21 @@ def box_median_depth(disp16, Q, boxes, minDisparity=0, box_image=None):
                                                (int(minDisparity) - 1) * 16, _ptr(bx), _ptr(bi), n, _ptr(out),
                                                _stream(dev)))
     return out if isinstance(disp16, torch.Tensor) else out.cpu().numpy()
+
+
+# ---------------------------------------------------------------- measurement hooks
+STAGE_NAMES = ("planes", "cost", "aggregate_pass1", "aggregate_pass2_select", "lrcheck_median", "speckle")
+
+
+def set_stage_timing(enable: bool, device=None) -> None:
+    """Record CUDA events between the stages of StereoSGBM.compute on this device's context."""
+    dev = _device_of() if device is None else int(device)
+    check(_lib.load().svb_set_timing(_lib.context(dev), int(bool(enable))))
+
+
+def last_stage_ms(device=None) -> dict:
+    """Per-stage device milliseconds of the last compute() (blocks until it has finished)."""
+    dev = _device_of() if device is None else int(device)
+    ms = (C.c_float * 6)()
+    check(_lib.load().svb_sgbm_last_stage_ms(_lib.context(dev), ms, 6))
+    return dict(zip(STAGE_NAMES, [float(v) for v in ms]))

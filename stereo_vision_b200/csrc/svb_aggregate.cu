@@ -399,13 +399,16 @@ static int launch_sweep(int safe, int NR, int G, const AggArgs &a, int ngrid, cu
     return safe ? launch_sweep_g<NV, PASS2, true>(NR, G, a, ngrid, st) : launch_sweep_g<NV, PASS2, false>(NR, G, a, ngrid, st);
 }
 
-int svb_launch_aggregate(svb_context *ctx, const SgbmPlan &pl, char *ws, size_t ws_stride, int B, cudaStream_t st)
+int svb_launch_aggregate(svb_context *ctx, const SgbmPlan &pl, char *ws, size_t ws_stride, int B, int passes,
+                         cudaStream_t st)
 {
     // reset schedulers / progress / scatter keys
+    if (passes & 1) {
     SVB_CUDA_CHECK(cudaMemsetAsync(ctx->tickets, 0, 2 * sizeof(unsigned), st));
     for (int b = 0; b < B; b++) {
         SVB_CUDA_CHECK(cudaMemsetAsync(ws + (size_t)b * ws_stride + pl.off_prog, 0, 2 * sizeof(unsigned) * pl.nbands, st));
         SVB_CUDA_CHECK(cudaMemsetAsync(ws + (size_t)b * ws_stride + pl.off_key, 0xFF, sizeof(unsigned) * (size_t)pl.H * pl.W, st));
+    }
     }
     AggArgs a;
     memset(&a, 0, sizeof a);
@@ -427,8 +430,9 @@ int svb_launch_aggregate(svb_context *ctx, const SgbmPlan &pl, char *ws, size_t 
     a.flip = 0;
     a.prog = (unsigned *)(ws + pl.off_prog);
     a.ticket = ctx->tickets;
-    int rc = launch_sweep<3, false>(pl.safe, NR, pl.G, a, pl.nbands * B, st);
-    if (rc) return rc;
+    int rc = SVB_OK;
+    if (passes & 1) rc = launch_sweep<3, false>(pl.safe, NR, pl.G, a, pl.nbands * B, st);
+    if (rc || !(passes & 2)) return rc;
     a.flip = 1;
     if (pl.p.mode == 1) {   // MODE_HH: right, down-right, down, down-left + selection
         a.prog = (unsigned *)(ws + pl.off_prog) + pl.nbands;

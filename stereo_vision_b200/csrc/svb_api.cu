@@ -38,6 +38,9 @@ extern "C" int svb_create(int device_id, svb_context **out)
     c->ws = nullptr;
     c->ws_bytes = 0;
     c->tickets = nullptr;
+    c->timing = 0;
+    c->ev_valid = 0;
+    for (int i = 0; i <= SVB_NUM_STAGES; i++) cudaEventCreate(&c->ev[i]);
     e = cudaMalloc(&c->tickets, 16 * sizeof(unsigned));
     if (e != cudaSuccess) {
         delete c;
@@ -54,6 +57,7 @@ extern "C" int svb_destroy(svb_context *ctx)
     cudaSetDevice(ctx->device);
     if (ctx->ws) cudaFree(ctx->ws);
     if (ctx->tickets) cudaFree(ctx->tickets);
+    for (int i = 0; i <= SVB_NUM_STAGES; i++) cudaEventDestroy(ctx->ev[i]);
     delete ctx;
     return SVB_OK;
 }
@@ -207,17 +211,48 @@ extern "C" int svb_sgbm_compute(svb_context *ctx, const svb_sgbm_params *raw, co
     cudaStream_t st = (cudaStream_t)stream;
     char *ws;
     if ((rc = get_workspace(ctx, pl.per_frame_bytes * (size_t)B, ws_user, ws_bytes, &ws))) return rc;
-    if ((rc = run_front(ctx, pl, left, right, pitch_bytes, image_stride_bytes, B, ws, st))) return rc;
-    if ((rc = svb_launch_aggregate(ctx, pl, ws, pl.per_frame_bytes, B, st))) return rc;
+#define SVB_MARK(i) do { if (ctx->timing) cudaEventRecord(ctx->ev[i], st); } while (0)
+    ctx->ev_valid = 0;
+    SVB_MARK(0);
+    if ((rc = svb_launch_planes(pl, left, right, pitch_bytes, image_stride_bytes, ws, pl.per_frame_bytes, B, st))) return rc;
+    SVB_MARK(1);
+    if ((rc = svb_launch_cost(pl, ws, pl.per_frame_bytes, B, st))) return rc;
+    SVB_MARK(2);
+    if ((rc = svb_launch_aggregate(ctx, pl, ws, pl.per_frame_bytes, B, 1, st))) return rc;
+    SVB_MARK(3);
+    if ((rc = svb_launch_aggregate(ctx, pl, ws, pl.per_frame_bytes, B, 2, st))) return rc;
+    SVB_MARK(4);
     if ((rc = svb_launch_lrcheck(pl, ws, pl.per_frame_bytes, B, st))) return rc;
     if ((rc = svb_launch_median3((const int16_t *)(ws + pl.off_dtmp), disp, H, W, W, pl.per_frame_bytes / 2,
                                  disp_pitch_elems, disp_stride_elems, B, st)))
         return rc;
+    SVB_MARK(5);
     if (pl.p.speckleWindowSize > 0)
         if ((rc = svb_launch_speckle(disp, H, W, disp_pitch_elems, disp_stride_elems, B, pl.invalid16,
                                      pl.p.speckleWindowSize, 16 * pl.p.speckleRange, (int32_t *)(ws + pl.off_labels),
                                      pl.per_frame_bytes / 4, st)))
             return rc;
+    SVB_MARK(6);
+    if (ctx->timing) ctx->ev_valid = 1;
+    return SVB_OK;
+}
+
+// Per-stage device times (ms) of the last svb_sgbm_compute on this context, measured with CUDA events recorded
+// on the caller's stream: [planes, cost, aggregate pass 1, aggregate pass 2 + selection, LR check + median,
+// speckle].  Blocks until that call has finished.  Enable with svb_set_timing(ctx, 1).
+extern "C" int svb_set_timing(svb_context *ctx, int enable)
+{
+    SVB_REQUIRE(ctx, SVB_ERR_INVALID, "set_timing: null context");
+    ctx->timing = enable;
+    ctx->ev_valid = 0;
+    return SVB_OK;
+}
+extern "C" int svb_sgbm_last_stage_ms(svb_context *ctx, float *ms, int n)
+{
+    SVB_REQUIRE(ctx && ms && n >= 6, SVB_ERR_INVALID, "last_stage_ms: need room for 6 floats");
+    SVB_REQUIRE(ctx->ev_valid, SVB_ERR_INVALID, "last_stage_ms: no timed svb_sgbm_compute on this context");
+    SVB_CUDA_CHECK(cudaEventSynchronize(ctx->ev[6]));
+    for (int i = 0; i < 6; i++) SVB_CUDA_CHECK(cudaEventElapsedTime(&ms[i], ctx->ev[i], ctx->ev[i + 1]));
     return SVB_OK;
 }
 
@@ -242,7 +277,7 @@ extern "C" int svb_sgbm_debug_stages(svb_context *ctx, const svb_sgbm_params *ra
             // for the tap we want the FINAL S, which pass 2 keeps in registers — so tap pass-1 S here and
             // let the test add the remaining directions' contribution through disp_raw parity instead.
         }
-        if ((rc = svb_launch_aggregate(ctx, pl, ws, pl.per_frame_bytes, 1, st))) return rc;
+        if ((rc = svb_launch_aggregate(ctx, pl, ws, pl.per_frame_bytes, 1, 3, st))) return rc;
         if (Svol) SVB_CUDA_CHECK(cudaMemcpyAsync(Svol, ws + pl.off_S, vol, cudaMemcpyDeviceToDevice, st));
         if (disp_raw) {
             if ((rc = svb_launch_lrcheck(pl, ws, pl.per_frame_bytes, 1, st))) return rc;

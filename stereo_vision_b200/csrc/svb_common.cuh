@@ -32,12 +32,16 @@ void svb_set_error(const char *fmt, ...);
         }                                 \
     } while (0)
 
+#define SVB_NUM_STAGES 7
 struct svb_context {
     int device;
     int num_sms;
     void *ws;          // grow-only cached workspace
     size_t ws_bytes;
     unsigned int *tickets;  // device counters for the sweep scheduler
+    int timing;             // record per-stage events in svb_sgbm_compute
+    cudaEvent_t ev[SVB_NUM_STAGES + 1];
+    int ev_valid;
 };
 
 // ---- resolved SGBM plan (host) ----
@@ -68,7 +72,9 @@ static inline size_t svb_align_up(size_t v, size_t a) { return (v + a - 1) / a *
 int svb_launch_planes(const SgbmPlan &pl, const uint8_t *left, const uint8_t *right, size_t pitch, size_t istride,
                       char *ws, size_t ws_stride, int B, cudaStream_t st);
 int svb_launch_cost(const SgbmPlan &pl, char *ws, size_t ws_stride, int B, cudaStream_t st);
-int svb_launch_aggregate(svb_context *ctx, const SgbmPlan &pl, char *ws, size_t ws_stride, int B, cudaStream_t st);
+// passes: bit 0 = pass 1 (4 forward paths), bit 1 = pass 2 (remaining paths + selection)
+int svb_launch_aggregate(svb_context *ctx, const SgbmPlan &pl, char *ws, size_t ws_stride, int B, int passes,
+                         cudaStream_t st);
 int svb_launch_lrcheck(const SgbmPlan &pl, char *ws, size_t ws_stride, int B, cudaStream_t st);
 int svb_launch_median3(const int16_t *src, int16_t *dst, int H, int W, size_t spitch, size_t sstride, size_t dpitch,
                        size_t dstride, int B, cudaStream_t st);

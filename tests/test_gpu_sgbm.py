@@ -87,7 +87,7 @@ def test_properties_at_full_size(sv):
     # the synthetic field is recovered on most valid pixels
     d_true = synth.disparity_field(L.shape[0], L.shape[1], D)
     ok = (np.abs(a / 16.0 - d_true) <= 1)[a != -16].mean()
-    assert ok > 0.95
+    assert ok > 0.9
 
 
 def test_error_behaviour(sv):

@@ -1,0 +1,78 @@
+"""CPU: pins the oracle (oracle/sv_oracle.c) against the committed cv2 4.13.0 golden vectors."""
+import hashlib
+
+import numpy as np
+import pytest
+
+import cases
+import oracle
+from stereo_vision_b200 import synth
+
+
+def _sha(a):
+    return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+
+
+def test_sgbm_small_sweep(golden):
+    for i, c in enumerate(cases.sgbm_small_cases()):
+        L, R = cases.sgbm_inputs(c)
+        key = np.frombuffer(bytes.fromhex(_sha(L)[:16] + _sha(R)[:16]), np.uint8)
+        assert np.array_equal(key, golden[f"sgbm_in_{i}"]), "seeded inputs not reproducible"
+        assert np.array_equal(oracle.sgbm_compute(L, R, **c["kw"]), golden[f"sgbm_{i}"]), (i, c)
+
+
+@pytest.mark.parametrize("name", ["c1", "c2"])
+def test_sgbm_full_size_hash(golden_full, name):
+    L, R, kw = cases.full_inputs(name)
+    assert [_sha(L), _sha(R)] == golden_full["full"][name]["in_sha256"]
+    assert _sha(oracle.sgbm_compute(L, R, **kw)) == golden_full["full"][name]["sha256"]
+
+
+def test_remap(golden):
+    for i, c in enumerate(cases.remap_cases()):
+        src, mx, my = cases.remap_inputs(c)
+        assert np.array_equal(oracle.remap(src, mx, my), golden[f"remap_{i}"])
+
+
+def test_maps(golden, golden_full):
+    q = lambda a: np.rint(a * np.float32(32)).astype(np.int32)
+    for (W, H) in [(640, 480), (1280, 720)]:
+        K1, d1, K2, d2, R, T = synth.synthetic_rig(W, H)
+        rect = golden[f"rect_{W}"]
+        R1, R2 = rect[0:9].reshape(3, 3), rect[9:18].reshape(3, 3)
+        P1, P2 = rect[18:30].reshape(3, 4), rect[30:42].reshape(3, 4)
+        for side, (K, d, Rr, P) in enumerate([(K1, d1, R1, P1), (K2, d2, R2, P2)]):
+            mx, my = oracle.init_undistort_rectify_map(K, d, Rr, P, (W, H))
+            assert [_sha(q(mx)), _sha(q(my))] == golden_full[f"mapq_{W}_{side}"]
+
+
+def test_post_filters(golden):
+    for j, arr in enumerate(cases.post_inputs()):
+        assert np.array_equal(oracle.median3(arr), golden[f"median_{j}"])
+        for (sz, df) in cases.SPECKLE_PARAMS:
+            assert np.array_equal(oracle.filter_speckles(arr, -16, sz, df), golden[f"speckle_{j}_{sz}_{df}"])
+
+
+def test_reproject(golden):
+    rng = np.random.default_rng(5)
+    Q = golden["rect_640"][-16:].reshape(4, 4)
+    disp = rng.integers(-16, 64 * 16, (480, 640)).astype(np.int16)
+    for hm in (0, 1):
+        for tag, d in (("s16", disp), ("f32", disp.astype(np.float32) / 16)):
+            got = oracle.reproject_to_3d(d, Q, bool(hm))[::4, ::4]
+            ref = golden[f"reproj_{tag}_{hm}"]
+            fin = np.isfinite(ref)
+            assert np.array_equal(np.isfinite(got), fin)
+            assert (np.abs(got[fin] - ref[fin]) / np.maximum(np.abs(ref[fin]), 1e-30)).max() <= 1e-5
+
+
+def test_box_median_semantics():
+    disp = np.full((20, 30), -16, np.int16)
+    disp[5:10, 5:10] = np.arange(25).reshape(5, 5) * 16 + 160
+    Q = np.array([[1, 0, 0, -15], [0, 1, 0, -10], [0, 0, 0, 500.0], [0, 0, 1 / 100.0, 0]])
+    out = oracle.box_median_depth(disp, Q, np.array([[5, 5, 10, 10], [0, 0, 4, 4], [4.5, 4.5, 6.2, 6.2]], np.float32), -16)
+    z = 500.0 / ((np.arange(25) + 10) / 100.0)
+    assert out[0] == np.float32(np.median(z.astype(np.float32)))
+    assert np.isnan(out[1])
+    sub = (disp[4:7, 4:7][disp[4:7, 4:7] != -16] / 16.0)
+    assert out[2] == np.float32(np.median((500.0 / (sub / 100.0)).astype(np.float32)))
