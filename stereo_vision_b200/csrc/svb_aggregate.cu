@@ -1,24 +1,36 @@
 // svb_aggregate.cu — SGM path aggregation (5-path MODE_SGBM, 8-path MODE_HH) + WTA / uniqueness / subpixel /
 // disp2 scatter.  Semantics: SURVEY.md §3.2.4-3.2.5 (cv2 4.13.0), bit-exact.
 //
-// Design (DESIGN.md §aggregation): ONE sweep kernel computes four path directions per pass as a wavefront.
+// Design (DESIGN.md §4.1): ONE sweep kernel computes four path directions per pass as a wavefront.
 //   * a "row-group" of G lanes owns one image row; each lane holds E=2*NR consecutive disparities as NR packed
 //     s16x2 registers.  The group walks its row in x; the horizontal path lives in registers.
 //   * row v trails row v-1 by two pixels, so the three vertical/diagonal predecessors (u-1,u,u+1 of row v-1) are
-//     already available; inside a CTA (a band of NGRP rows) they travel through a 4-slot shared-memory ring, and
-//     between bands through a small global edge buffer with acquire/release progress counters.  Bands take
-//     tickets in launch order, so a band only ever waits for one that is already running (no deadlock).
-//   * the cost volume C is read exactly once per pass, S is written once (pass 1) and read once (pass 2): the
-//     four directions of a pass accumulate in registers.
+//     already available.  Inside a CTA (a band of NGRP rows) they travel through a 4-slot shared-memory ring whose
+//     slot index is the step number mod 4 — the step loop is unrolled by 4, so every ring address is an
+//     immediate.  Each ring vector is preceded by a 16-byte pad holding P2, which is the d=-1 / d=D halo of the
+//     recurrence, so the neighbour taps are plain unconditional LDS.
+//   * between bands the three states travel through a global edge buffer.  A dedicated DMA warp per CTA polls the
+//     producer band's progress counter (ld.acquire), pulls the edge vectors EDGE_PF pixels ahead into an 8-slot
+//     "row -1" ring with cp.async, and publishes this band's own progress (st.release) — all off the compute
+//     warps' critical path.  Bands take tickets in launch order, so a band only ever waits for one that is
+//     already running (no deadlock, no cooperative launch).
+//   * C (and S in pass 2) are prefetched PFD pixels ahead into registers; C is read exactly once per pass,
+//     S written once (pass 1) / read once (pass 2): the four directions of a pass accumulate in registers.
+//   * the loop body is branch-free: out-of-grid predecessors are zero vectors selected by pointer, inactive
+//     steps compute on clamped addresses with their stores predicated off.
 //   * recurrence in normalised form: with Lc = min(Lprev - minLprev, P2),
 //         L(d) = C(d) + min(Lc(d), min(Lc(d-1), Lc(d+1)) + P1)          (== cv2's formula)
 //     -> per packed pair: PRMT, VIMNMX, VIADDMNMX, IADD, IADD(S), 1/2 VIMNMX3, VIADDMNMX(normalise+clamp).
-//   * pass 2 (reverse sweep) adds its four directions to S from pass 1 and selects the disparity in-register.
+//   * pass 2 (reverse sweep) adds its four directions to S from pass 1 and selects the disparity in-register;
+//     the per-pixel scalars (min S, best d, second-best S, subpixel taps) are parked one pixel per lane and the
+//     scalar tail (uniqueness test, subpixel division, disp2 scatter, store) runs lane-parallel every G pixels.
 #include "svb_common.cuh"
 
-#define AGG_NGRP 16        // rows per band (row-groups per CTA)
 #define AGG_SLOTS 4        // ring depth (u-1, u, u+1 live + one being written)
+#define AGG_ENS 8          // slots of the cross-band "row -1" ring
+#define AGG_EPF 4          // cross-band prefetch distance (pixels)
 #define AGG_PUB 8          // publish cross-band progress every AGG_PUB pixels
+#define AGG_PADE 8         // int16 elements of P2 halo in front of every ring vector
 
 struct AggArgs {
     const int16_t *C;      // [H][W1][Dp]
@@ -34,7 +46,6 @@ struct AggArgs {
     int flip;              // 0: rows top-down, x ascending; 1: both reversed
     uint32_t P1d, P2d;     // duplicated halves
     int uniq, invalid16;
-    int has_pad;
 };
 
 __device__ __forceinline__ unsigned ld_acquire(const unsigned *p)
@@ -47,6 +58,14 @@ __device__ __forceinline__ void st_release(unsigned *p, unsigned v)
 {
     asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
+__device__ __forceinline__ void cp_async16(void *smem, const void *gmem)
+{
+    const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
 template <int G>
 __device__ __forceinline__ uint32_t group_min_u32(uint32_t v)
@@ -68,7 +87,7 @@ __device__ __forceinline__ uint32_t lane_min16(const uint32_t (&L)[NR])
 }
 
 // one direction: prev (clamped, normalised) Lc in p[], neighbour words wprev (hi half = Lc[d0-1]) and
-// wnext (lo half = Lc[d0+E]).  Produces L[], returns nothing; caller reduces.
+// wnext (lo half = Lc[d0+E]).  Produces L[].
 template <int NR>
 __device__ __forceinline__ void dir_update(const uint32_t (&p)[NR], uint32_t wprev, uint32_t wnext,
                                            const uint32_t (&c)[NR], uint32_t P1d, uint32_t (&L)[NR])
@@ -86,9 +105,9 @@ __device__ __forceinline__ void dir_update(const uint32_t (&p)[NR], uint32_t wpr
     }
 }
 
-template <int NR, int G, bool SAFE>
-__device__ __forceinline__ void finish_dir(uint32_t (&L)[NR], uint32_t (&s)[NR], uint32_t P2d, const uint32_t (&keep)[NR],
-                                           int has_pad)
+// add L into S, then normalise L in place: Lc = min(L - min_d L, P2) (padded disparities forced to P2)
+template <int NR, int G, bool SAFE, bool PAD>
+__device__ __forceinline__ void finish_dir(uint32_t (&L)[NR], uint32_t (&s)[NR], uint32_t P2d, const uint32_t (&keep)[NR])
 {
     const uint32_t minL = group_min_u32<G>(lane_min16<NR>(L));
     const uint32_t negd = ((0u - minL) & 0xFFFFu) * 0x10001u;
@@ -96,16 +115,14 @@ __device__ __forceinline__ void finish_dir(uint32_t (&L)[NR], uint32_t (&s)[NR],
     for (int k = 0; k < NR; k++) {
         if (SAFE) s[k] += L[k];
         else s[k] = __viaddmin_u16x2(s[k], L[k], 0x7FFF7FFFu);
-        L[k] = __viaddmin_s16x2(L[k], negd, P2d);   // Lc = min(L - minL, P2)
+        L[k] = __viaddmin_s16x2(L[k], negd, P2d);
     }
-    if (has_pad) {
+    if (PAD) {
 #pragma unroll
         for (int k = 0; k < NR; k++) L[k] = (L[k] & keep[k]) | (P2d & ~keep[k]);
     }
 }
 
-template <int NR> struct VecT;
-template <> struct VecT<4> { typedef uint4 T; };
 template <int NR>
 __device__ __forceinline__ void ld_regs_shared(const int16_t *p, uint32_t (&r)[NR])
 {
@@ -132,15 +149,6 @@ __device__ __forceinline__ void ld_regs_stream(const int16_t *p, uint32_t (&r)[N
     }
 }
 template <int NR>
-__device__ __forceinline__ void ld_regs_cg(const int16_t *p, uint32_t (&r)[NR])
-{
-#pragma unroll
-    for (int q = 0; q < NR / 4; q++) {
-        const uint4 v = __ldcg(reinterpret_cast<const uint4 *>(p) + q);
-        r[4 * q] = v.x; r[4 * q + 1] = v.y; r[4 * q + 2] = v.z; r[4 * q + 3] = v.w;
-    }
-}
-template <int NR>
 __device__ __forceinline__ void st_regs_cg(int16_t *p, const uint32_t (&r)[NR])
 {
 #pragma unroll
@@ -155,75 +163,211 @@ __device__ __forceinline__ void st_regs_stream(int16_t *p, const uint32_t (&r)[N
         __stcs(reinterpret_cast<uint4 *>(p) + q, make_uint4(r[4 * q], r[4 * q + 1], r[4 * q + 2], r[4 * q + 3]));
 }
 
-// ---- disparity selection for one pixel (first loop).  s[] = final S, clamped to 0x7FFF,
-// padded disparities forced to 0x7FFF.  All lanes of the warp must call (warp collectives inside). ----
-template <int NR, int G>
-__device__ __forceinline__ void wta_select(const uint32_t (&s)[NR], int lane, const AggArgs &a, int16_t *scratch,
-                                           int16_t *dpre, unsigned *keys, int x_full, int y, bool active)
+// ---- pass-2 tail, lane-parallel: lane holds one parked pixel (first loop) ----
+__device__ __forceinline__ void select_flush(const AggArgs &a, int16_t *dpre, unsigned *keys, int y, int x_full,
+                                             uint32_t best, uint32_t s2, uint32_t taps)
 {
-    constexpr int E = 2 * NR;
-    const uint32_t d0 = (uint32_t)lane * E;
-    uint32_t key[E];
-#pragma unroll
-    for (int k = 0; k < NR; k++) {
-        key[2 * k] = __byte_perm(s[k], d0 + 2 * k, 0x1054);       // (S_lo << 16) | d
-        key[2 * k + 1] = __byte_perm(s[k], d0 + 2 * k + 1, 0x3254);   // (S_hi << 16) | d
-    }
-    uint32_t lk = key[0];
-#pragma unroll
-    for (int k = 1; k < E; k++) lk = min(lk, key[k]);
-    const uint32_t best = group_min_u32<G>(lk);
     const int minS = (int)(best >> 16), bestD = (int)(best & 0xFFFFu);
     bool fail = minS >= 32767;   // all costs saturated: cv2 ends with bestDisp=-1 -> INVALID
-    if (a.uniq > 0) {
-        uint32_t lk2 = 0xFFFFFFFFu;
-#pragma unroll
-        for (int k = 0; k < E; k++) {
-            const uint32_t kk = ((uint32_t)((int)d0 + k - bestD + 1) <= 2u) ? 0xFFFFFFFFu : key[k];
-            lk2 = min(lk2, kk);
+    if (a.uniq > 0) fail = fail || ((int)s2 * (100 - a.uniq) < minS * 100);
+    int out = a.invalid16;
+    if (!fail) {
+        const int x2 = x_full - bestD - a.minD;
+        atomicMin(keys + (size_t)y * a.W + x2, ((unsigned)minS << 16) | (unsigned)(0xFFFF - x_full));
+        int d16 = bestD * 16;
+        if (bestD > 0 && bestD < a.D - 1) {
+            const int sm1 = (int)(taps & 0xFFFFu), sp1 = (int)(taps >> 16);
+            const int denom2 = max(sm1 + sp1 - 2 * minS, 1);
+            d16 += ((sm1 - sp1) * 16 + denom2) / (denom2 * 2);
         }
-        const int S2 = (int)(group_min_u32<G>(lk2) >> 16);
-        fail = fail || (S2 * (100 - a.uniq) < minS * 100);
+        out = d16 + a.minD * 16;
     }
-    // subpixel taps through shared memory
-    st_regs<NR>(scratch + lane * E, s);
-    __syncwarp();
-    if (lane == 0 && active) {
-        int out = a.invalid16;
-        if (!fail) {
-            const int x2 = x_full - bestD - a.minD;
-            atomicMin(keys + (size_t)y * a.W + x2, ((unsigned)minS << 16) | (unsigned)(0xFFFF - x_full));
-            int d16 = bestD * 16;
-            if (bestD > 0 && bestD < a.D - 1) {
-                const int sm1 = scratch[bestD - 1], sp1 = scratch[bestD + 1];
-                const int denom2 = max(sm1 + sp1 - 2 * minS, 1);
-                d16 += ((sm1 - sp1) * 16 + denom2) / (denom2 * 2);
-            }
-            out = d16 + a.minD * 16;
-        }
-        dpre[(size_t)y * a.W + x_full] = (int16_t)out;
-    }
-    __syncwarp();
+    dpre[(size_t)y * a.W + x_full] = (int16_t)out;
 }
 
-// NV = 3: wavefront sweep with the three vertical/diagonal predecessors; NV = 0: horizontal path only
-// (rows independent; used for the 5th path of MODE_SGBM).
-template <int NR, int G, int NV, bool PASS2, bool SAFE>
-__global__ void __launch_bounds__(AGG_NGRP *G) k_sweep(const AggArgs a)
+// Shared-memory geometry of one CTA (int16 elements)
+template <int NGRP, int NV, bool PASS2>
+struct SweepSmem {
+    __host__ __device__ static int vs(int Dp) { return Dp + AGG_PADE; }
+    __host__ __device__ static int nvec() { return NV ? NGRP * AGG_SLOTS * 3 + AGG_ENS * 3 + 1 : 0; }
+    __host__ __device__ static int ring_elems(int Dp) { return NV ? nvec() * vs(Dp) + AGG_PADE : 0; }
+    __host__ __device__ static int scratch_elems(int Dp) { return PASS2 ? NGRP * 2 * Dp : 0; }
+    __host__ __device__ static int mask_elems(int E) { return PASS2 ? (E + 4) * E : 0; }
+    __host__ __device__ static size_t bytes(int Dp, int E)
+    {
+        return 2 * (size_t)(ring_elems(Dp) + scratch_elems(Dp) + mask_elems(E)) + 16;
+    }
+};
+
+#define AGG_UNROLL 8
+
+// Per-thread state of a compute lane.  All arrays are indexed by compile-time constants only.
+template <int NR, int G, int NGRP, int NV, bool PASS2, bool SAFE, bool PAD, int PFD>
+struct SweepLane {
+    static constexpr int E = 2 * NR;
+    // loop-invariant
+    int W1, Dp, VS, lag, lane, y, xdir, xbase;      // x = xbase + xdir*u
+    bool rowActive, isRow0;
+    uint32_t P1d, P2d;
+    uint32_t keep[NR];
+    const int16_t *Crow;        // + lane*E, row y
+    int16_t *Srow;
+    const int16_t *prevL;       // ring vectors of row g-1 (data start + lane*E); rowm1 ring for g == 0
+    int16_t *ownL;              // ring vectors of row g
+    const int16_t *zeroL;
+    int16_t *edge_out;          // + lane*E, or nullptr
+    int16_t *scratch;           // pass 2: 2*Dp per group
+    const int16_t *masktab;
+    // loop-carried
+    uint32_t h[NR];
+    uint32_t cbuf[PFD][NR], sbuf[PFD][NR];
+    uint32_t cap_best, cap_s2, cap_taps;
+
+    __device__ __forceinline__ void prefetch(int slot, int upf)
+    {
+        const int xp = xbase + xdir * min(max(upf, 0), W1 - 1);
+        const size_t off = (size_t)xp * Dp;
+        switch (slot) {   // slot is a compile-time constant at every call site
+#define SVB_PF_CASE(i)                                             \
+    case i:                                                        \
+        if (i < PFD) {                                             \
+            ld_regs_stream<NR>(Crow + off, cbuf[i < PFD ? i : 0]); \
+            if (PASS2) ld_regs_stream<NR>(Srow + off, sbuf[i < PFD ? i : 0]); \
+        }                                                          \
+        break;
+            SVB_PF_CASE(0) SVB_PF_CASE(1) SVB_PF_CASE(2) SVB_PF_CASE(3)
+#undef SVB_PF_CASE
+        }
+    }
+
+    template <int PH>
+    __device__ __forceinline__ void step(const AggArgs &a, int t, int16_t *dpre, unsigned *keys)
+    {
+        constexpr int PB = PH % PFD;
+        const int u = t - lag;
+        const bool act = rowActive && (unsigned)u < (unsigned)W1;
+        uint32_t c[NR], s[NR], L[NR];
+#pragma unroll
+        for (int k = 0; k < NR; k++) { c[k] = cbuf[PB][k]; s[k] = PASS2 ? sbuf[PB][k] : 0u; }
+        prefetch(PB, u + PFD);
+        // ---- horizontal path (registers) ----
+        {
+            const uint32_t hm = u > 0 ? 0xFFFFFFFFu : 0u;
+#pragma unroll
+            for (int k = 0; k < NR; k++) h[k] &= hm;
+            uint32_t wprev = __shfl_up_sync(0xffffffffu, h[NR - 1], 1, G);
+            uint32_t wnext = __shfl_down_sync(0xffffffffu, h[0], 1, G);
+            if (lane == 0) wprev = P2d;
+            if (lane == G - 1) wnext = P2d;
+            dir_update<NR>(h, wprev, wnext, c, P1d, L);
+            finish_dir<NR, G, SAFE, PAD>(L, s, P2d, keep);
+#pragma unroll
+            for (int k = 0; k < NR; k++) h[k] = L[k];
+        }
+        // ---- vertical / diagonal paths: predecessors (u-1, u, u+1) of the previous row ----
+        if (NV) {
+#pragma unroll
+            for (int j = 0; j < 3; j++) {
+                constexpr int dummy = 0; (void)dummy;
+                const int offv = (((PH + 1 + j) & (AGG_SLOTS - 1)) * 3 + j) * VS;          // written 3-j steps ago
+                const int offe = (((PH + AGG_ENS - 1 + j) & (AGG_ENS - 1)) * 3 + j) * VS;  // pixel u-1+j, u == t
+                const int16_t *src = prevL + (isRow0 ? offe : offv);
+                if (j == 2 && u + 1 >= W1) src = zeroL;
+                uint32_t p[NR];
+                ld_regs_shared<NR>(src, p);
+                const uint32_t wprev = *reinterpret_cast<const uint32_t *>(src - 2);
+                const uint32_t wnext = *reinterpret_cast<const uint32_t *>(src + E);
+                dir_update<NR>(p, wprev, wnext, c, P1d, L);
+                finish_dir<NR, G, SAFE, PAD>(L, s, P2d, keep);
+                if (act) {
+                    st_regs<NR>(ownL + ((PH & (AGG_SLOTS - 1)) * 3 + j) * VS, L);
+                    if (edge_out) st_regs_cg<NR>(edge_out + ((size_t)u * 3 + j) * Dp, L);
+                }
+            }
+        }
+        if (!PASS2) {
+            if (act) {
+                if (!SAFE) {
+#pragma unroll
+                    for (int k = 0; k < NR; k++) s[k] = __vminu2(s[k], 0x7FFF7FFFu);
+                }
+                st_regs_stream<NR>(Srow + (size_t)(xbase + xdir * u) * Dp, s);
+            }
+        } else {
+#pragma unroll
+            for (int k = 0; k < NR; k++) {
+                if (PAD) s[k] |= 0x7FFF7FFFu & ~keep[k];
+                s[k] = __vminu2(s[k], 0x7FFF7FFFu);
+            }
+            // winner: first d attaining min S  (key = S<<16 | d)
+            const uint32_t d0 = (uint32_t)lane * E;
+            uint32_t lk = 0xFFFFFFFFu;
+#pragma unroll
+            for (int k = 0; k < NR; k++) {
+                lk = min(lk, __byte_perm(s[k], d0 + 2 * k, 0x1054));       // (S_lo << 16) | d
+                lk = min(lk, __byte_perm(s[k], d0 + 2 * k + 1, 0x3254));   // (S_hi << 16) | d
+            }
+            const uint32_t best = group_min_u32<G>(lk);
+            const int bestD = (int)(best & 0xFFFFu);
+            // second-best S outside bestD-1..bestD+1 (mask table indexed by bestD relative to this lane)
+            uint32_t s2 = 0;
+            if (a.uniq > 0) {
+                const int ti = min(max(bestD - (int)d0 + 2, 0), E + 3);
+                uint32_t mk[NR], sm[NR];
+                ld_regs_shared<NR>(masktab + ti * E, mk);
+#pragma unroll
+                for (int k = 0; k < NR; k++) sm[k] = s[k] | mk[k];
+                s2 = group_min_u32<G>(lane_min16<NR>(sm));
+            }
+            // subpixel taps through shared memory (double-buffered per group)
+            int16_t *sc = scratch + (PH & 1) * Dp;
+            st_regs<NR>(sc + lane * E, s);
+            __syncwarp();
+            const uint32_t sm1 = (uint16_t)sc[max(bestD - 1, 0)];
+            const uint32_t sp1 = (uint16_t)sc[min(bestD + 1, Dp - 1)];
+            if (lane == (u & (G - 1))) { cap_best = best; cap_s2 = s2; cap_taps = sm1 | (sp1 << 16); }
+            if (act && ((u & (G - 1)) == G - 1 || u == W1 - 1)) {
+                const int ul = (u & ~(G - 1)) + lane;
+                if (ul <= u) select_flush(a, dpre, keys, y, xbase + xdir * ul + a.minX1, cap_best, cap_s2, cap_taps);
+            }
+        }
+    }
+};
+
+__device__ __forceinline__ void cta_barrier() { asm volatile("bar.sync 0;" ::: "memory"); }
+
+// NV = 3: wavefront sweep with the three vertical/diagonal predecessors (+ one DMA warp per CTA);
+// NV = 0: horizontal path only (rows independent; the 5th path of MODE_SGBM), no barriers, no DMA warp.
+template <int NR, int G, int NGRP, int NV, bool PASS2, bool SAFE, bool PAD, int PFD>
+__global__ void __launch_bounds__(NGRP *G + (NV ? 32 : 0)) k_sweep(const __grid_constant__ AggArgs a)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
+    typedef SweepSmem<NGRP, NV, PASS2> SM;
     constexpr int E = 2 * NR;
-    const int Dp = a.Dp;
+    constexpr int NCOMP = NGRP * G;
+    const int Dp = a.Dp, W1 = a.W1, VS = SM::vs(Dp);
     int16_t *ring = reinterpret_cast<int16_t *>(smem_raw);
-    int16_t *scratch_base = ring + (NV ? (size_t)AGG_NGRP * AGG_SLOTS * 3 * Dp : 0);
+    int16_t *scratch_base = ring + SM::ring_elems(Dp);
+    int16_t *masktab = scratch_base + SM::scratch_elems(Dp);
     __shared__ unsigned s_ticket;
-    const int tid = threadIdx.x, g = tid / G, lane = tid % G;
+    const int tid = threadIdx.x;
     unsigned ticket = blockIdx.x;
     if (NV) {
         if (tid == 0) s_ticket = atomicAdd(a.ticket, 1u);
-        __syncthreads();
-        ticket = s_ticket;
+        // ring: data 0, pads P2; (the barrier below also publishes s_ticket)
+        const int n = SM::ring_elems(Dp);
+        const int16_t p2 = (int16_t)(a.P2d & 0xFFFFu);
+        for (int i = tid; i < n; i += blockDim.x) ring[i] = (i % VS) < AGG_PADE ? p2 : (int16_t)0;
     }
+    if (PASS2) {
+        // mask table: entry ti <-> r = ti-2 = bestD - d0; element e is masked (0x7FFF) iff |e - r| <= 1
+        for (int i = tid; i < (E + 4) * E; i += blockDim.x) {
+            const int r = i / E - 2, e = i % E;
+            masktab[i] = (e >= r - 1 && e <= r + 1) ? (int16_t)0x7FFF : (int16_t)0;
+        }
+    }
+    __syncthreads();
+    if (NV) ticket = s_ticket;
     const int frame = ticket / a.nbands, band = ticket % a.nbands;
     const size_t fo = (size_t)frame * a.ws_stride;
     const int16_t *Cv = reinterpret_cast<const int16_t *>(reinterpret_cast<const char *>(a.C) + fo);
@@ -232,171 +376,143 @@ __global__ void __launch_bounds__(AGG_NGRP *G) k_sweep(const AggArgs a)
     unsigned *prog = reinterpret_cast<unsigned *>(reinterpret_cast<char *>(a.prog) + fo);
     int16_t *dpre = reinterpret_cast<int16_t *>(reinterpret_cast<char *>(a.dpre) + fo);
     unsigned *keys = reinterpret_cast<unsigned *>(reinterpret_cast<char *>(a.keys) + fo);
+    const size_t edge_band = (size_t)W1 * 3 * Dp;
+    int16_t *rowm1 = ring + (size_t)NGRP * AGG_SLOTS * 3 * VS;          // vectors [ENS][3]
+    int16_t *zerov = rowm1 + (size_t)AGG_ENS * 3 * VS;
+    const int lag_last = 2 * (NGRP - 1);
+    const int nsteps = (W1 + (NV ? lag_last : 0) + AGG_UNROLL - 1) / AGG_UNROLL * AGG_UNROLL;
 
-    const int v = band * AGG_NGRP + g;
-    const bool rowActive = v < a.H;
-    const int y = a.flip ? a.H - 1 - v : v;
-    const size_t rowoff = (size_t)(rowActive ? y : 0) * a.W1 * Dp + lane * E;
-    const int16_t *Crow = Cv + rowoff;
-    int16_t *Srow = Sv + rowoff;
-    uint32_t keep[NR];
-#pragma unroll
-    for (int k = 0; k < NR; k++)
-        keep[k] = ((lane * E + 2 * k < a.D) ? 0x0000FFFFu : 0u) | ((lane * E + 2 * k + 1 < a.D) ? 0xFFFF0000u : 0u);
-    const uint32_t P1d = a.P1d, P2d = a.P2d;
-    int16_t *ring_g = ring + (size_t)g * AGG_SLOTS * 3 * Dp;
-    const int16_t *ring_prev = ring + (size_t)(g > 0 ? g - 1 : 0) * AGG_SLOTS * 3 * Dp;
-    int16_t *scratch = scratch_base + (size_t)g * Dp;
-    const size_t edge_band = (size_t)a.W1 * 3 * Dp;
-    const int16_t *edge_in = band > 0 ? edge + (size_t)(band - 1) * edge_band : nullptr;
-    int16_t *edge_out = (NV && band + 1 < a.nbands && g == AGG_NGRP - 1) ? edge + (size_t)band * edge_band : nullptr;
-    const bool publisher = NV && (band + 1 < a.nbands) && tid == AGG_NGRP * G - 1;
-
-    uint32_t h[NR], cn[NR], sn[NR];
-#pragma unroll
-    for (int k = 0; k < NR; k++) { h[k] = 0; cn[k] = 0; sn[k] = 0; }
-    const int lag = NV ? 2 * g : 0;
-    const int nsteps = a.W1 + (NV ? 2 * (AGG_NGRP - 1) : 0);
-    unsigned known = 0;
-    // prefetch for the first step of group 0
-    if (rowActive && lag == 0) {
-        const int x0 = a.flip ? a.W1 - 1 : 0;
-        ld_regs_stream<NR>(Crow + (size_t)x0 * Dp, cn);
-        if (PASS2) ld_regs_stream<NR>(Srow + (size_t)x0 * Dp, sn);
-    }
-    for (int t = 0; t < nsteps; t++) {
-        const int u = t - lag;
-        const bool active = rowActive && u >= 0 && u < a.W1;
-        if (NV) {
-            if (tid == 0 && band > 0 && t < a.W1) {
-                const unsigned need = (unsigned)min(t + 2, a.W1);
-                while (known < need) known = ld_acquire(prog + band - 1);
+    if (NV && tid >= NCOMP) {
+        // ================= DMA warp: cross-band hand-off =================
+        const int lane = tid - NCOMP;
+        const bool consumer = band > 0, producer = band + 1 < a.nbands;
+        const int16_t *edge_in = edge + (size_t)(consumer ? band - 1 : 0) * edge_band;
+        const unsigned *prog_in = prog + (consumer ? band - 1 : 0);
+        const int cpv = Dp / 8;            // 16-byte chunks per vector
+        const int nch = 3 * cpv;
+        unsigned known = 0;
+        auto fetch = [&](int pe) {         // pixel pe of the producer band's last row -> row -1 ring
+            const int16_t *src = edge_in + (size_t)pe * 3 * Dp;
+            int16_t *dst = rowm1 + (size_t)((pe & (AGG_ENS - 1)) * 3) * VS + AGG_PADE;
+            for (int i = lane; i < nch; i += 32) {
+                const int j = i / cpv, k = i - j * cpv;
+                cp_async16(dst + j * VS + k * 8, src + i * 8);
             }
-            __syncthreads();
-            if (publisher) {
-                const int done = t - 2 * (AGG_NGRP - 1);
-                if (done > 0 && (done % AGG_PUB) == 0) {
+        };
+        auto wait_for = [&](unsigned need) {
+            if (lane == 0)
+                while (known < need) known = ld_acquire(prog_in);
+            __syncwarp();
+        };
+        if (consumer) {
+            const int n0 = min(AGG_EPF, W1);
+            wait_for((unsigned)n0);
+            for (int pe = 0; pe < n0; pe++) fetch(pe);
+        }
+        cp_async_commit();
+        cp_async_wait<0>();
+        for (int t = 0; t < nsteps; t++) {
+            const int pe = t + AGG_EPF;
+            if (consumer && pe < W1) {
+                wait_for((unsigned)(pe + 1));
+                fetch(pe);
+            }
+            cp_async_commit();
+            cp_async_wait<AGG_EPF - 1>();
+            cta_barrier();
+            if (producer && lane == 0) {
+                const int done = t - lag_last;   // pixels of the last row finished before this barrier
+                if (done > 0 && done < W1 && (done % AGG_PUB) == 0) {
                     __threadfence();
                     st_release(prog + band, (unsigned)done);
                 }
             }
         }
-        const int x = a.flip ? a.W1 - 1 - u : u;
-        uint32_t c[NR], s[NR];
-#pragma unroll
-        for (int k = 0; k < NR; k++) { c[k] = cn[k]; s[k] = PASS2 ? sn[k] : 0u; }
-        {   // prefetch next pixel of this row
-            const int un = u + 1;
-            if (rowActive && un >= 0 && un < a.W1) {
-                const int xn = a.flip ? a.W1 - 1 - un : un;
-                ld_regs_stream<NR>(Crow + (size_t)xn * Dp, cn);
-                if (PASS2) ld_regs_stream<NR>(Srow + (size_t)xn * Dp, sn);
-            }
-        }
-        uint32_t L[NR];
-        // ---- horizontal path (registers) ----
-        {
-            if (u <= 0) {
-#pragma unroll
-                for (int k = 0; k < NR; k++) h[k] = 0;
-            }
-            uint32_t wprev = __shfl_up_sync(0xffffffffu, h[NR - 1], 1);
-            uint32_t wnext = __shfl_down_sync(0xffffffffu, h[0], 1);
-            if (lane == 0) wprev = P2d;
-            if (lane == G - 1) wnext = P2d;
-            dir_update<NR>(h, wprev, wnext, c, P1d, L);
-            finish_dir<NR, G, SAFE>(L, s, P2d, keep, a.has_pad);
-#pragma unroll
-            for (int k = 0; k < NR; k++) h[k] = L[k];
-        }
-        // ---- vertical / diagonal paths: predecessors (u-1, u, u+1) of the previous row ----
-        if (NV) {
-#pragma unroll
-            for (int j = 0; j < 3; j++) {
-                const int uu = u - 1 + j;
-                uint32_t p[NR], wprev = 0, wnext = 0;
-#pragma unroll
-                for (int k = 0; k < NR; k++) p[k] = 0;
-                if (active && v > 0 && uu >= 0 && uu < a.W1) {
-                    if (g > 0) {
-                        const int16_t *src = ring_prev + (size_t)((uu & (AGG_SLOTS - 1)) * 3 + j) * Dp + lane * E;
-                        ld_regs_shared<NR>(src, p);
-                        wprev = lane > 0 ? *reinterpret_cast<const uint32_t *>(src - 2) : P2d;
-                        wnext = lane < G - 1 ? *reinterpret_cast<const uint32_t *>(src + E) : P2d;
-                    } else {
-                        const int16_t *src = edge_in + ((size_t)uu * 3 + j) * Dp + lane * E;
-                        ld_regs_cg<NR>(src, p);
-                        wprev = lane > 0 ? __ldcg(reinterpret_cast<const uint32_t *>(src - 2)) : P2d;
-                        wnext = lane < G - 1 ? __ldcg(reinterpret_cast<const uint32_t *>(src + E)) : P2d;
-                    }
-                }
-                dir_update<NR>(p, wprev, wnext, c, P1d, L);
-                finish_dir<NR, G, SAFE>(L, s, P2d, keep, a.has_pad);
-                if (active) {
-                    st_regs<NR>(ring_g + (size_t)((u & (AGG_SLOTS - 1)) * 3 + j) * Dp + lane * E, L);
-                    if (edge_out) st_regs_cg<NR>(edge_out + ((size_t)u * 3 + j) * Dp + lane * E, L);
-                }
-            }
-        }
-        if (!PASS2) {
-            if (active) {
-                if (!SAFE) {
-#pragma unroll
-                    for (int k = 0; k < NR; k++) s[k] = __vminu2(s[k], 0x7FFF7FFFu);
-                }
-                st_regs_stream<NR>(Srow + (size_t)x * Dp, s);
-            }
-        } else {
-#pragma unroll
-            for (int k = 0; k < NR; k++) {
-                if (a.has_pad) s[k] |= 0x7FFF7FFFu & ~keep[k];
-                s[k] = __vminu2(s[k], 0x7FFF7FFFu);
-            }
-            wta_select<NR, G>(s, lane, a, scratch, dpre, keys, x + a.minX1, y, active);
-        }
-    }
-    if (NV && (band + 1 < a.nbands)) {
-        __syncthreads();
-        if (publisher) {
+        cta_barrier();
+        if (producer && lane == 0) {
             __threadfence();
-            st_release(prog + band, (unsigned)a.W1);
+            st_release(prog + band, (unsigned)W1);
         }
+        return;
     }
+
+    // ================= compute lanes =================
+    SweepLane<NR, G, NGRP, NV, PASS2, SAFE, PAD, PFD> st;
+    const int g = tid / G, lane = tid % G;
+    const int v = band * NGRP + g;
+    st.W1 = W1; st.Dp = Dp; st.VS = VS; st.lane = lane;
+    st.lag = NV ? 2 * g : 0;
+    st.rowActive = v < a.H;
+    st.isRow0 = (g == 0);
+    st.y = a.flip ? a.H - 1 - v : v;
+    st.xdir = a.flip ? -1 : 1;
+    st.xbase = a.flip ? W1 - 1 : 0;
+    st.P1d = a.P1d; st.P2d = a.P2d;
+#pragma unroll
+    for (int k = 0; k < NR; k++)
+        st.keep[k] = ((lane * E + 2 * k < a.D) ? 0x0000FFFFu : 0u) | ((lane * E + 2 * k + 1 < a.D) ? 0xFFFF0000u : 0u);
+    const size_t rowoff = (size_t)(st.rowActive ? st.y : 0) * W1 * Dp + lane * E;
+    st.Crow = Cv + rowoff;
+    st.Srow = Sv + rowoff;
+    st.ownL = ring + (size_t)(g * AGG_SLOTS * 3) * VS + AGG_PADE + lane * E;
+    st.prevL = (g == 0 ? rowm1 : ring + (size_t)((g - 1) * AGG_SLOTS * 3) * VS) + AGG_PADE + lane * E;
+    st.zeroL = zerov + AGG_PADE + lane * E;
+    st.edge_out = (NV && band + 1 < a.nbands && g == NGRP - 1) ? edge + (size_t)band * edge_band + lane * E : nullptr;
+    st.scratch = scratch_base + (size_t)g * 2 * Dp;
+    st.masktab = masktab;
+    st.cap_best = 0; st.cap_s2 = 0; st.cap_taps = 0;
+#pragma unroll
+    for (int k = 0; k < NR; k++) st.h[k] = 0;
+#pragma unroll
+    for (int i = 0; i < PFD; i++) st.prefetch(i, i - st.lag);
+
+    for (int t0 = 0; t0 < nsteps; t0 += AGG_UNROLL) {
+#define SVB_STEP(PH)                 \
+    if (NV) cta_barrier();           \
+    st.template step<PH>(a, t0 + PH, dpre, keys);
+        SVB_STEP(0) SVB_STEP(1) SVB_STEP(2) SVB_STEP(3) SVB_STEP(4) SVB_STEP(5) SVB_STEP(6) SVB_STEP(7)
+#undef SVB_STEP
+    }
+    if (NV) cta_barrier();
 }
 
 // ---------------- host side ----------------
-template <int NR, int G, int NV, bool PASS2, bool SAFE>
+template <int NR, int G, int NGRP, int NV, bool PASS2, bool SAFE, bool PAD>
 static int launch_sweep_t(const AggArgs &a, int ngrid, cudaStream_t st)
 {
-    const size_t smem = (NV ? (size_t)AGG_NGRP * AGG_SLOTS * 3 * a.Dp * 2 : 0) + (PASS2 ? (size_t)AGG_NGRP * a.Dp * 2 : 0);
-    auto kern = k_sweep<NR, G, NV, PASS2, SAFE>;
+    constexpr int PFD = NR == 4 ? 4 : 2;
+    const size_t smem = SweepSmem<NGRP, NV, PASS2>::bytes(a.Dp, 2 * NR);
+    auto kern = k_sweep<NR, G, NGRP, NV, PASS2, SAFE, PAD, PFD>;
     static size_t configured = 0;
     if (smem > configured) {
         SVB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         configured = smem;
     }
-    kern<<<ngrid, AGG_NGRP * G, smem, st>>>(a);
+    kern<<<ngrid, NGRP * G + (NV ? 32 : 0), smem, st>>>(a);
     SVB_CUDA_CHECK(cudaGetLastError());
     return SVB_OK;
 }
 
-template <int NV, bool PASS2, bool SAFE>
+template <int NV, bool PASS2, bool SAFE, bool PAD>
 static int launch_sweep_g(int NR, int G, const AggArgs &a, int ngrid, cudaStream_t st)
 {
-    if (NR == 8) return launch_sweep_t<8, 32, NV, PASS2, SAFE>(a, ngrid, st);
+    if (NR == 8) return launch_sweep_t<8, 32, 7, NV, PASS2, SAFE, PAD>(a, ngrid, st);
     switch (G) {
-    case 2: return launch_sweep_t<4, 2, NV, PASS2, SAFE>(a, ngrid, st);
-    case 4: return launch_sweep_t<4, 4, NV, PASS2, SAFE>(a, ngrid, st);
-    case 8: return launch_sweep_t<4, 8, NV, PASS2, SAFE>(a, ngrid, st);
-    case 16: return launch_sweep_t<4, 16, NV, PASS2, SAFE>(a, ngrid, st);
-    default: return launch_sweep_t<4, 32, NV, PASS2, SAFE>(a, ngrid, st);
+    case 2: return launch_sweep_t<4, 2, 16, NV, PASS2, SAFE, PAD>(a, ngrid, st);
+    case 4: return launch_sweep_t<4, 4, 16, NV, PASS2, SAFE, PAD>(a, ngrid, st);
+    case 8: return launch_sweep_t<4, 8, 16, NV, PASS2, SAFE, PAD>(a, ngrid, st);
+    case 16: return launch_sweep_t<4, 16, 16, NV, PASS2, SAFE, PAD>(a, ngrid, st);
+    default: return launch_sweep_t<4, 32, 15, NV, PASS2, SAFE, PAD>(a, ngrid, st);
     }
 }
 
 template <int NV, bool PASS2>
-static int launch_sweep(int safe, int NR, int G, const AggArgs &a, int ngrid, cudaStream_t st)
+static int launch_sweep(int safe, int pad, int NR, int G, const AggArgs &a, int ngrid, cudaStream_t st)
 {
-    return safe ? launch_sweep_g<NV, PASS2, true>(NR, G, a, ngrid, st) : launch_sweep_g<NV, PASS2, false>(NR, G, a, ngrid, st);
+    if (safe) return pad ? launch_sweep_g<NV, PASS2, true, true>(NR, G, a, ngrid, st)
+                         : launch_sweep_g<NV, PASS2, true, false>(NR, G, a, ngrid, st);
+    return pad ? launch_sweep_g<NV, PASS2, false, true>(NR, G, a, ngrid, st)
+               : launch_sweep_g<NV, PASS2, false, false>(NR, G, a, ngrid, st);
 }
 
 int svb_launch_aggregate(svb_context *ctx, const SgbmPlan &pl, char *ws, size_t ws_stride, int B, int passes,
@@ -404,11 +520,11 @@ int svb_launch_aggregate(svb_context *ctx, const SgbmPlan &pl, char *ws, size_t 
 {
     // reset schedulers / progress / scatter keys
     if (passes & 1) {
-    SVB_CUDA_CHECK(cudaMemsetAsync(ctx->tickets, 0, 2 * sizeof(unsigned), st));
-    for (int b = 0; b < B; b++) {
-        SVB_CUDA_CHECK(cudaMemsetAsync(ws + (size_t)b * ws_stride + pl.off_prog, 0, 2 * sizeof(unsigned) * pl.nbands, st));
-        SVB_CUDA_CHECK(cudaMemsetAsync(ws + (size_t)b * ws_stride + pl.off_key, 0xFF, sizeof(unsigned) * (size_t)pl.H * pl.W, st));
-    }
+        SVB_CUDA_CHECK(cudaMemsetAsync(ctx->tickets, 0, 2 * sizeof(unsigned), st));
+        for (int b = 0; b < B; b++) {
+            SVB_CUDA_CHECK(cudaMemsetAsync(ws + (size_t)b * ws_stride + pl.off_prog, 0, 2 * sizeof(unsigned) * pl.nbands, st));
+            SVB_CUDA_CHECK(cudaMemsetAsync(ws + (size_t)b * ws_stride + pl.off_key, 0xFF, sizeof(unsigned) * (size_t)pl.H * pl.W, st));
+        }
     }
     AggArgs a;
     memset(&a, 0, sizeof a);
@@ -424,22 +540,22 @@ int svb_launch_aggregate(svb_context *ctx, const SgbmPlan &pl, char *ws, size_t 
     a.P2d = (uint32_t)pl.p.P2 * 0x10001u;
     a.uniq = pl.p.uniquenessRatio;
     a.invalid16 = pl.invalid16;
-    a.has_pad = pl.Dp != pl.D;
+    const int pad = pl.Dp != pl.D;
     const int NR = pl.E / 2;
     // pass 1: left, up-left, up, up-right
     a.flip = 0;
     a.prog = (unsigned *)(ws + pl.off_prog);
     a.ticket = ctx->tickets;
     int rc = SVB_OK;
-    if (passes & 1) rc = launch_sweep<3, false>(pl.safe, NR, pl.G, a, pl.nbands * B, st);
+    if (passes & 1) rc = launch_sweep<3, false>(pl.safe, pad, NR, pl.G, a, pl.nbands * B, st);
     if (rc || !(passes & 2)) return rc;
     a.flip = 1;
     if (pl.p.mode == 1) {   // MODE_HH: right, down-right, down, down-left + selection
         a.prog = (unsigned *)(ws + pl.off_prog) + pl.nbands;
         a.ticket = ctx->tickets + 1;
-        rc = launch_sweep<3, true>(pl.safe, NR, pl.G, a, pl.nbands * B, st);
+        rc = launch_sweep<3, true>(pl.safe, pad, NR, pl.G, a, pl.nbands * B, st);
     } else {                // MODE_SGBM: 5th path (from the right) + selection, rows independent
-        rc = launch_sweep<0, true>(pl.safe, NR, pl.G, a, pl.nbands * B, st);
+        rc = launch_sweep<0, true>(pl.safe, pad, NR, pl.G, a, pl.nbands * B, st);
     }
     return rc;
 }

@@ -125,7 +125,7 @@ int svb_make_plan(const svb_sgbm_params *raw, int H, int W, int ch, SgbmPlan *pl
         pl->G = 32;
     }
     pl->Dp = pl->E * pl->G;
-    pl->NG = 16;
+    pl->NG = pl->G == 32 ? (pl->E == 16 ? 7 : 15) : 16;   // rows per band (must match the k_sweep instantiation)
     pl->nbands = (H + pl->NG - 1) / pl->NG;
     pl->Wr = (int)svb_align_up((size_t)W + pl->Dp + 8, 8);
     size_t off = 0;
