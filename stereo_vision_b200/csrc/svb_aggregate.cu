@@ -368,7 +368,9 @@ __global__ void __launch_bounds__(NGRP *G + (NV ? 32 : 0)) k_sweep(const __grid_
     }
     __syncthreads();
     if (NV) ticket = s_ticket;
-    const int frame = ticket / a.nbands, band = ticket % a.nbands;
+    // band-major ticket order: consecutive bands of one frame start B tickets apart, so with enough frames in
+    // flight a band's producer is already well ahead when the band gets an SM (no SM is held by a waiting band)
+    const int frame = ticket % a.B, band = ticket / a.B;
     const size_t fo = (size_t)frame * a.ws_stride;
     const int16_t *Cv = reinterpret_cast<const int16_t *>(reinterpret_cast<const char *>(a.C) + fo);
     int16_t *Sv = reinterpret_cast<int16_t *>(reinterpret_cast<char *>(a.S) + fo);
