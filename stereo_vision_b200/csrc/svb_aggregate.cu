@@ -155,6 +155,31 @@ __device__ __forceinline__ void st_regs_cg(int16_t *p, const uint32_t (&r)[NR])
     for (int q = 0; q < NR / 4; q++)
         __stcg(reinterpret_cast<uint4 *>(p) + q, make_uint4(r[4 * q], r[4 * q + 1], r[4 * q + 2], r[4 * q + 3]));
 }
+// predicated 16-byte global stores (no branch: keeps the four directions of a step in one basic block)
+__device__ __forceinline__ void st_cg_pred(void *p, uint32_t a, uint32_t b, uint32_t c, uint32_t d, bool pred)
+{
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.s32 p, %5, 0;\n\t@p st.global.cg.v4.u32 [%0], {%1, %2, %3, %4};\n\t}"
+                 ::"l"(p), "r"(a), "r"(b), "r"(c), "r"(d), "r"((int)pred) : "memory");
+}
+__device__ __forceinline__ void st_cs_pred(void *p, uint32_t a, uint32_t b, uint32_t c, uint32_t d, bool pred)
+{
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.s32 p, %5, 0;\n\t@p st.global.cs.v4.u32 [%0], {%1, %2, %3, %4};\n\t}"
+                 ::"l"(p), "r"(a), "r"(b), "r"(c), "r"(d), "r"((int)pred) : "memory");
+}
+template <int NR>
+__device__ __forceinline__ void st_regs_cg_pred(int16_t *p, const uint32_t (&r)[NR], bool pred)
+{
+#pragma unroll
+    for (int q = 0; q < NR / 4; q++)
+        st_cg_pred(reinterpret_cast<uint4 *>(p) + q, r[4 * q], r[4 * q + 1], r[4 * q + 2], r[4 * q + 3], pred);
+}
+template <int NR>
+__device__ __forceinline__ void st_regs_cs_pred(int16_t *p, const uint32_t (&r)[NR], bool pred)
+{
+#pragma unroll
+    for (int q = 0; q < NR / 4; q++)
+        st_cs_pred(reinterpret_cast<uint4 *>(p) + q, r[4 * q], r[4 * q + 1], r[4 * q + 2], r[4 * q + 3], pred);
+}
 template <int NR>
 __device__ __forceinline__ void st_regs_stream(int16_t *p, const uint32_t (&r)[NR])
 {
@@ -189,7 +214,7 @@ __device__ __forceinline__ void select_flush(const AggArgs &a, int16_t *dpre, un
 template <int NGRP, int NV, bool PASS2>
 struct SweepSmem {
     __host__ __device__ static int vs(int Dp) { return Dp + AGG_PADE; }
-    __host__ __device__ static int nvec() { return NV ? NGRP * AGG_SLOTS * 3 + AGG_ENS * 3 + 1 : 0; }
+    __host__ __device__ static int nvec() { return NV ? NGRP * AGG_SLOTS * 3 + AGG_ENS * 3 + 1 + AGG_SLOTS * 3 : 0; }
     __host__ __device__ static int ring_elems(int Dp) { return NV ? nvec() * vs(Dp) + AGG_PADE : 0; }
     __host__ __device__ static int scratch_elems(int Dp) { return PASS2 ? NGRP * 2 * Dp : 0; }
     __host__ __device__ static int mask_elems(int E) { return PASS2 ? (E + 4) * E : 0; }
@@ -215,6 +240,7 @@ struct SweepLane {
     const int16_t *prevL;       // ring vectors of row g-1 (data start + lane*E); rowm1 ring for g == 0
     int16_t *ownL;              // ring vectors of row g
     const int16_t *zeroL;
+    int16_t *trashL;            // ring-shaped scratch row: where inactive steps park their (meaningless) vectors
     int16_t *edge_out;          // + lane*E, or nullptr
     int16_t *scratch;           // pass 2: 2*Dp per group
     const int16_t *masktab;
@@ -266,9 +292,11 @@ struct SweepLane {
         }
         // ---- vertical / diagonal paths: predecessors (u-1, u, u+1) of the previous row ----
         if (NV) {
+            int16_t *wbase = act ? ownL : trashL;
+            const bool epred = act && edge_out != nullptr;
+            int16_t *eptr = edge_out + (size_t)(act ? u : 0) * 3 * Dp;
 #pragma unroll
             for (int j = 0; j < 3; j++) {
-                constexpr int dummy = 0; (void)dummy;
                 const int offv = (((PH + 1 + j) & (AGG_SLOTS - 1)) * 3 + j) * VS;          // written 3-j steps ago
                 const int offe = (((PH + AGG_ENS - 1 + j) & (AGG_ENS - 1)) * 3 + j) * VS;  // pixel u-1+j, u == t
                 const int16_t *src = prevL + (isRow0 ? offe : offv);
@@ -279,20 +307,16 @@ struct SweepLane {
                 const uint32_t wnext = *reinterpret_cast<const uint32_t *>(src + E);
                 dir_update<NR>(p, wprev, wnext, c, P1d, L);
                 finish_dir<NR, G, SAFE, PAD>(L, s, P2d, keep);
-                if (act) {
-                    st_regs<NR>(ownL + ((PH & (AGG_SLOTS - 1)) * 3 + j) * VS, L);
-                    if (edge_out) st_regs_cg<NR>(edge_out + ((size_t)u * 3 + j) * Dp, L);
-                }
+                st_regs<NR>(wbase + ((PH & (AGG_SLOTS - 1)) * 3 + j) * VS, L);
+                st_regs_cg_pred<NR>(eptr + j * Dp, L, epred);
             }
         }
         if (!PASS2) {
-            if (act) {
-                if (!SAFE) {
+            if (!SAFE) {
 #pragma unroll
-                    for (int k = 0; k < NR; k++) s[k] = __vminu2(s[k], 0x7FFF7FFFu);
-                }
-                st_regs_stream<NR>(Srow + (size_t)(xbase + xdir * u) * Dp, s);
+                for (int k = 0; k < NR; k++) s[k] = __vminu2(s[k], 0x7FFF7FFFu);
             }
+            st_regs_cs_pred<NR>(Srow + (size_t)(xbase + xdir * (act ? u : 0)) * Dp, s, act);
         } else {
 #pragma unroll
             for (int k = 0; k < NR; k++) {
@@ -310,8 +334,8 @@ struct SweepLane {
             const uint32_t best = group_min_u32<G>(lk);
             const int bestD = (int)(best & 0xFFFFu);
             // second-best S outside bestD-1..bestD+1 (mask table indexed by bestD relative to this lane)
-            uint32_t s2 = 0;
-            if (a.uniq > 0) {
+            uint32_t s2;
+            {
                 const int ti = min(max(bestD - (int)d0 + 2, 0), E + 3);
                 uint32_t mk[NR], sm[NR];
                 ld_regs_shared<NR>(masktab + ti * E, mk);
@@ -459,6 +483,7 @@ __global__ void __launch_bounds__(NGRP *G + (NV ? 32 : 0)) k_sweep(const __grid_
     st.ownL = ring + (size_t)(g * AGG_SLOTS * 3) * VS + AGG_PADE + lane * E;
     st.prevL = (g == 0 ? rowm1 : ring + (size_t)((g - 1) * AGG_SLOTS * 3) * VS) + AGG_PADE + lane * E;
     st.zeroL = zerov + AGG_PADE + lane * E;
+    st.trashL = zerov + VS + AGG_PADE + lane * E;
     st.edge_out = (NV && band + 1 < a.nbands && g == NGRP - 1) ? edge + (size_t)band * edge_band + lane * E : nullptr;
     st.scratch = scratch_base + (size_t)g * 2 * Dp;
     st.masktab = masktab;

@@ -186,7 +186,11 @@ __global__ void __launch_bounds__(256) k_ccl_count(int *__restrict__ L, int H, i
     if (l < 0) return;
     int r = uf_find(Lb, i);
     Lb[i] = r;   // benign race: only ever shortens chains towards the same root
-    atomicAdd(&Sz[r], 1);
+    // warp-aggregated count: lanes that share a root elect one leader (large components would otherwise
+    // serialise ~W*H same-address atomics in L2)
+    const unsigned act = __activemask();
+    const unsigned same = __match_any_sync(act, r);
+    if ((int)(__ffs(same) - 1) == (int)(threadIdx.x & 31)) atomicAdd(&Sz[r], __popc(same));
 }
 
 __global__ void __launch_bounds__(256) k_ccl_paint(int16_t *__restrict__ img, const int *__restrict__ L, int H, int W,
