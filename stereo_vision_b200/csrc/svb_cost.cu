@@ -4,9 +4,9 @@
 //   k_planes : u8 images -> per-pixel BT operands, already widened to packed s16x2 so the cost kernel's inner
 //              loop is pure DPX/VIADD work:
 //                left  LP[y][pl][xi]          = uint4 { (u,u), (255-u,255-u), (u0,u0), (255-u1,255-u1) }
-//                right RP[y][pl][arr][copy][] = int16 arrays V, 255-V, V0, 255-V1 stored REVERSED in x
-//                                               (index j = W-1-x), two copies offset by one element so that a
-//                                               run of disparities starting at any j is 4-byte aligned.
+//                right RP[y][pl][copy 8][arr 4][Wr+8] = int16 arrays V, 255-V, V0, 255-V1 stored REVERSED in x
+//                                               (index j = W-1-x); copy c holds element j at position j-c+8, so a
+//                                               run of 8 disparities starting at any j is one aligned LDG.128.
 //   k_cost_h : BT pixel cost for 8 disparities per thread (4 packed registers), running horizontal box sum
 //              along x in registers -> Hs[y][xi][Dp]
 //   k_cost_v : running vertical box sum of Hs -> C, padded disparities overwritten with CPAD
@@ -40,68 +40,76 @@ __device__ __forceinline__ void bt_triplet(int pm, int p, int pp, bool has_l, bo
 }
 __device__ __forceinline__ uint32_t dup16(int v) { return (uint32_t)v * 0x10001u; }
 
-// one thread per (image column j in reversed order, row); handles left and right image, all planes
-__global__ void __launch_bounds__(128) k_planes(const uint8_t *__restrict__ left, const uint8_t *__restrict__ right,
-                                                int H, int W, int C, size_t pitch, size_t istride, int ftzero,
-                                                int minX1, int W1, int Wr, uint4 *__restrict__ LP,
-                                                int16_t *__restrict__ RP, size_t ws_stride)
+// One CTA per image row.  Per plane: plane values of both images are staged in shared memory once, the left BT
+// operands go out as one uint4 per column, the right operands are built reversed in x in shared memory and then
+// written as 8 copies, copy c shifted so that a disparity run starting at reversed index j0 with j0 % 8 == c is
+// 16-byte aligned: the cost kernel reads every right operand with one coalesced LDG.128 per lane.
+//   RP[y][plane][copy c][array a][Wr8],  element j of array a sits at position j - c + 8 of copy c.
+#define PLANES_THREADS 256
+__global__ void __launch_bounds__(PLANES_THREADS) k_planes(const uint8_t *__restrict__ left, const uint8_t *__restrict__ right,
+                                                           int H, int W, int C, size_t pitch, size_t istride, int ftzero,
+                                                           int minX1, int W1, int Wr, uint4 *__restrict__ LP,
+                                                           int16_t *__restrict__ RP, size_t ws_stride)
 {
-    const int j = blockIdx.x * blockDim.x + threadIdx.x;   // reversed right index / also used as left x
-    const int y = blockIdx.y, b = blockIdx.z;
+    extern __shared__ __align__(16) unsigned char psm[];
+    const int Wa = Wr + 16;                                   // staged array length (8 zeros in front, >= 8 behind)
+    int16_t *A = reinterpret_cast<int16_t *>(psm);            // [4][Wa]
+    uint8_t *pvL = psm + (size_t)4 * Wa * 2;                  // [W]
+    uint8_t *pvR = pvL + ((W + 15) & ~15);                    // [W]
+    const int y = blockIdx.x, b = blockIdx.y, tid = threadIdx.x;
     const int NPL = 2 * C;
+    const int Wr8 = Wr + 8;
     left += (size_t)b * istride;
     right += (size_t)b * istride;
     LP = reinterpret_cast<uint4 *>(reinterpret_cast<char *>(LP) + (size_t)b * ws_stride);
     RP = reinterpret_cast<int16_t *>(reinterpret_cast<char *>(RP) + (size_t)b * ws_stride);
     const int yn = max(y - 1, 0), ys = min(y + 1, H - 1);
-    // ---- left: x = j ----
-    if (j >= minX1 && j < minX1 + W1) {
-        const int x = j;
-        const uint8_t *rc = left + (size_t)y * pitch, *rn = left + (size_t)yn * pitch, *rs = left + (size_t)ys * pitch;
-        for (int ch = 0; ch < C; ch++) {
-            int lo, hi;
-            int g = grad_at(rc, rn, rs, x, W, C, ch, ftzero);
-            bt_triplet(x > 0 ? grad_at(rc, rn, rs, x - 1, W, C, ch, ftzero) : 0, g,
-                       x < W - 1 ? grad_at(rc, rn, rs, x + 1, W, C, ch, ftzero) : 0, x > 0, x < W - 1, lo, hi);
-            LP[((size_t)y * NPL + 2 * ch) * W1 + (x - minX1)] = make_uint4(dup16(g), dup16(255 - g), dup16(lo), dup16(255 - hi));
-            int it = inten_at(rc, x, W, C, ch, ftzero);
-            bt_triplet(x > 0 ? inten_at(rc, x - 1, W, C, ch, ftzero) : 0, it,
-                       x < W - 1 ? inten_at(rc, x + 1, W, C, ch, ftzero) : 0, x > 0, x < W - 1, lo, hi);
-            LP[((size_t)y * NPL + 2 * ch + 1) * W1 + (x - minX1)] = make_uint4(dup16(it), dup16(255 - it), dup16(lo), dup16(255 - hi));
+    const uint8_t *lc = left + (size_t)y * pitch, *ln = left + (size_t)yn * pitch, *ls = left + (size_t)ys * pitch;
+    const uint8_t *rc = right + (size_t)y * pitch, *rn = right + (size_t)yn * pitch, *rs = right + (size_t)ys * pitch;
+    for (int pl = 0; pl < NPL; pl++) {
+        const int ch = pl >> 1;
+        __syncthreads();   // previous plane's readers are done with A / pv
+        for (int x = tid; x < W; x += PLANES_THREADS) {
+            pvL[x] = (uint8_t)((pl & 1) ? inten_at(lc, x, W, C, ch, ftzero) : grad_at(lc, ln, ls, x, W, C, ch, ftzero));
+            pvR[x] = (uint8_t)((pl & 1) ? inten_at(rc, x, W, C, ch, ftzero) : grad_at(rc, rn, rs, x, W, C, ch, ftzero));
         }
-    }
-    // ---- right: element j <-> x = W-1-j; positions j (copy 0) and j+1 (copy 1) ----
-    if (j < Wr - 1) {
-        const int x = W - 1 - j;
-        const uint8_t *rc = right + (size_t)y * pitch, *rn = right + (size_t)yn * pitch, *rs = right + (size_t)ys * pitch;
-        for (int pl = 0; pl < NPL; pl++) {
+        __syncthreads();
+        // left operands
+        for (int xi = tid; xi < W1; xi += PLANES_THREADS) {
+            const int x = xi + minX1;
+            int lo, hi;
+            const int p = pvL[x];
+            bt_triplet(x > 0 ? pvL[x - 1] : 0, p, x < W - 1 ? pvL[x + 1] : 0, x > 0, x < W - 1, lo, hi);
+            LP[((size_t)y * NPL + pl) * W1 + xi] = make_uint4(dup16(p), dup16(255 - p), dup16(lo), dup16(255 - hi));
+        }
+        // right operands, reversed: staged index j + 8 <-> x = W-1-j
+        for (int i = tid; i < Wa; i += PLANES_THREADS) {
+            const int x = W - 1 - (i - 8);
             int v = 0, vn = 0, v0 = 0, v1n = 0;
-            if (x >= 0) {
-                const int ch = pl >> 1;
-                int p, pm, pp, lo, hi;
-                if (pl & 1) {
-                    p = inten_at(rc, x, W, C, ch, ftzero);
-                    pm = x > 0 ? inten_at(rc, x - 1, W, C, ch, ftzero) : 0;
-                    pp = x < W - 1 ? inten_at(rc, x + 1, W, C, ch, ftzero) : 0;
-                } else {
-                    p = grad_at(rc, rn, rs, x, W, C, ch, ftzero);
-                    pm = x > 0 ? grad_at(rc, rn, rs, x - 1, W, C, ch, ftzero) : 0;
-                    pp = x < W - 1 ? grad_at(rc, rn, rs, x + 1, W, C, ch, ftzero) : 0;
-                }
-                bt_triplet(pm, p, pp, x > 0, x < W - 1, lo, hi);
+            if (i >= 8 && x >= 0) {
+                int lo, hi;
+                const int p = pvR[x];
+                bt_triplet(x > 0 ? pvR[x - 1] : 0, p, x < W - 1 ? pvR[x + 1] : 0, x > 0, x < W - 1, lo, hi);
                 v = p; vn = 255 - p; v0 = lo; v1n = 255 - hi;
             }
-            int16_t *base = RP + ((size_t)y * NPL + pl) * 8 * Wr;   // [arr 4][copy 2][Wr]
-            base[(0 * 2 + 0) * Wr + j] = (int16_t)v;   base[(0 * 2 + 1) * Wr + j + 1] = (int16_t)v;
-            base[(1 * 2 + 0) * Wr + j] = (int16_t)vn;  base[(1 * 2 + 1) * Wr + j + 1] = (int16_t)vn;
-            base[(2 * 2 + 0) * Wr + j] = (int16_t)v0;  base[(2 * 2 + 1) * Wr + j + 1] = (int16_t)v0;
-            base[(3 * 2 + 0) * Wr + j] = (int16_t)v1n; base[(3 * 2 + 1) * Wr + j + 1] = (int16_t)v1n;
-            if (j == 0) {
-                base[(0 * 2 + 1) * Wr] = 0; base[(1 * 2 + 1) * Wr] = 0; base[(2 * 2 + 1) * Wr] = 0; base[(3 * 2 + 1) * Wr] = 0;
-            }
-            if (j == Wr - 2) {
-                base[(0 * 2 + 0) * Wr + Wr - 1] = 0; base[(1 * 2 + 0) * Wr + Wr - 1] = 0;
-                base[(2 * 2 + 0) * Wr + Wr - 1] = 0; base[(3 * 2 + 0) * Wr + Wr - 1] = 0;
+            A[i] = (int16_t)v; A[Wa + i] = (int16_t)vn; A[2 * Wa + i] = (int16_t)v0; A[3 * Wa + i] = (int16_t)v1n;
+        }
+        __syncthreads();
+        // 8 shifted copies, 16 bytes per store
+        const int nq = Wr8 / 8;
+        int16_t *outp = RP + ((size_t)y * NPL + pl) * 32 * Wr8;
+        for (int i = tid; i < 4 * nq; i += PLANES_THREADS) {
+            const int a = i / nq, q = i - a * nq;
+            const uint4 va = *reinterpret_cast<const uint4 *>(A + (size_t)a * Wa + 8 * q);
+            const uint4 vb = *reinterpret_cast<const uint4 *>(A + (size_t)a * Wa + 8 * q + 8);
+            const uint32_t w[8] = {va.x, va.y, va.z, va.w, vb.x, vb.y, vb.z, vb.w};
+#pragma unroll
+            for (int c = 0; c < 8; c++) {
+                uint32_t o[4];
+#pragma unroll
+                for (int k = 0; k < 4; k++)
+                    o[k] = (c & 1) ? __byte_perm(w[c / 2 + k], w[c / 2 + k + 1], 0x5432) : w[c / 2 + k];
+                *reinterpret_cast<uint4 *>(outp + ((size_t)c * 4 + a) * Wr8 + 8 * q) = make_uint4(o[0], o[1], o[2], o[3]);
             }
         }
     }
@@ -110,39 +118,47 @@ __global__ void __launch_bounds__(128) k_planes(const uint8_t *__restrict__ left
 int svb_launch_planes(const SgbmPlan &pl, const uint8_t *left, const uint8_t *right, size_t pitch, size_t istride,
                       char *ws, size_t ws_stride, int B, cudaStream_t st)
 {
-    dim3 grid((pl.Wr + 127) / 128, pl.H, B);
-    k_planes<<<grid, 128, 0, st>>>(left, right, pl.H, pl.W, pl.ch, pitch, istride, pl.ftzero, pl.minX1, pl.W1, pl.Wr,
-                                   (uint4 *)(ws + pl.off_lplanes), (int16_t *)(ws + pl.off_rplanes), ws_stride);
+    dim3 grid(pl.H, B);
+    const size_t smem = (size_t)4 * (pl.Wr + 16) * 2 + 2 * (size_t)((pl.W + 15) & ~15);
+    static size_t configured = 0;
+    if (smem > 48 * 1024 && smem > configured) {
+        SVB_CUDA_CHECK(cudaFuncSetAttribute(k_planes, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured = smem;
+    }
+    k_planes<<<grid, PLANES_THREADS, smem, st>>>(left, right, pl.H, pl.W, pl.ch, pitch, istride, pl.ftzero, pl.minX1,
+                                                 pl.W1, pl.Wr, (uint4 *)(ws + pl.off_lplanes),
+                                                 (int16_t *)(ws + pl.off_rplanes), ws_stride);
     SVB_CUDA_CHECK(cudaGetLastError());
     return SVB_OK;
 }
 
 // pixel cost for 8 disparities (4 packed regs) at cost column xc of row y
 template <int NPL>
-__device__ __forceinline__ void pix8(const uint4 *__restrict__ LProw, const int16_t *__restrict__ RProw, int W1, int Wr,
+__device__ __forceinline__ void pix8(const uint4 *__restrict__ LProw, const int16_t *__restrict__ RProw, int W1, int Wr8,
                                      int xc, int jb0, int lane8, uint32_t (&acc)[4])
 {
-    // jb = (W-1-x+minD) with x = xc+minX1  ->  jb0 - xc
+    // reversed right index of disparity 0 of this lane: jb = (W-1-x+minD) with x = xc+minX1  ->  jb0 - xc
     const int j0 = jb0 - xc + lane8;
-    const int cpy = j0 & 1;
-    const int pos = j0 + cpy;
+    const int cpy = j0 & 7;                       // copy whose position of j0 is 16-byte aligned
+    const int16_t *rb = RProw + (size_t)cpy * 4 * Wr8 + (j0 - cpy + 8);
 #pragma unroll
     for (int i = 0; i < 4; i++) acc[i] = 0;
 #pragma unroll
     for (int pl = 0; pl < NPL; pl++) {
         const uint4 Lw = __ldg(LProw + (size_t)pl * W1 + xc);
-        const int16_t *rb = RProw + (size_t)pl * 8 * Wr + (size_t)cpy * Wr + pos;
-        const uint32_t *pV = reinterpret_cast<const uint32_t *>(rb);
-        const uint32_t *pVn = reinterpret_cast<const uint32_t *>(rb + 2 * Wr);
-        const uint32_t *pV0 = reinterpret_cast<const uint32_t *>(rb + 4 * Wr);
-        const uint32_t *pV1n = reinterpret_cast<const uint32_t *>(rb + 6 * Wr);
+        const int16_t *rp = rb + (size_t)pl * 32 * Wr8;
+        const uint4 V = __ldg(reinterpret_cast<const uint4 *>(rp));
+        const uint4 Vn = __ldg(reinterpret_cast<const uint4 *>(rp + Wr8));
+        const uint4 V0 = __ldg(reinterpret_cast<const uint4 *>(rp + 2 * Wr8));
+        const uint4 V1n = __ldg(reinterpret_cast<const uint4 *>(rp + 3 * Wr8));
+        const uint32_t v[4] = {V.x, V.y, V.z, V.w}, vn[4] = {Vn.x, Vn.y, Vn.z, Vn.w};
+        const uint32_t v0[4] = {V0.x, V0.y, V0.z, V0.w}, v1n[4] = {V1n.x, V1n.y, V1n.z, V1n.w};
 #pragma unroll
         for (int i = 0; i < 4; i++) {
-            const uint32_t V = __ldg(pV + i), Vn = __ldg(pVn + i), V0 = __ldg(pV0 + i), V1n = __ldg(pV1n + i);
-            const uint32_t Bv = __vadd2(V0, Lw.y);                 // v0 + (255-u)
-            const uint32_t X = __viaddmax_s16x2(Lw.x, V1n, Bv);    // max(u + 255-v1, .)
-            const uint32_t Ev = __vadd2(Lw.z, Vn);                 // u0 + (255-v)
-            const uint32_t Y = __viaddmax_s16x2(V, Lw.w, Ev);      // max(v + 255-u1, .)
+            const uint32_t Bv = __vadd2(v0[i], Lw.y);                 // v0 + (255-u)
+            const uint32_t X = __viaddmax_s16x2(Lw.x, v1n[i], Bv);    // max(u + 255-v1, .)
+            const uint32_t Ev = __vadd2(Lw.z, vn[i]);                 // u0 + (255-v)
+            const uint32_t Y = __viaddmax_s16x2(v[i], Lw.w, Ev);      // max(v + 255-u1, .)
             uint32_t c = __viaddmax_s16x2_relu(__vmins2(X, Y), 0xFF01FF01u, 0u);   // max(min-255, 0)
             if (pl & 1) c = (c >> 2) & 0x3FFF3FFFu;
             acc[i] = __vadd2(acc[i], c);
@@ -167,7 +183,8 @@ __global__ void __launch_bounds__(256) k_cost_h(const uint4 *__restrict__ LP, co
     RP = reinterpret_cast<const int16_t *>(reinterpret_cast<const char *>(RP) + (size_t)b * ws_stride);
     Hs = reinterpret_cast<int16_t *>(reinterpret_cast<char *>(Hs) + (size_t)b * ws_stride);
     const uint4 *LProw = LP + (size_t)y * NPL * W1;
-    const int16_t *RProw = RP + (size_t)y * NPL * 8 * Wr;
+    const int Wr8 = Wr + 8;
+    const int16_t *RProw = RP + (size_t)y * NPL * 32 * Wr8;
     uint4 *out = reinterpret_cast<uint4 *>(Hs + ((size_t)y * W1) * Dp + lane * 8);
     const size_t ostride = Dp / 8;   // uint4 per column
     uint32_t ring[BS][4];
@@ -182,7 +199,7 @@ __global__ void __launch_bounds__(256) k_cost_h(const uint4 *__restrict__ LP, co
             const int k = k0 + i;
             const int xc = max(0, min(W1 - 1, k));
             uint32_t p[4];
-            pix8<NPL>(LProw, RProw, W1, Wr, xc, jb0, lane * 8, p);
+            pix8<NPL>(LProw, RProw, W1, Wr8, xc, jb0, lane * 8, p);
 #pragma unroll
             for (int q = 0; q < 4; q++) {
                 sum[q] = sum[q] + p[q] - ring[i][q];   // per-half: no carry/borrow (sum>=ring, totals < 2^15)
