@@ -7,16 +7,16 @@
 //                right RP[y][pl][copy 8][arr 4][Wr+8] = int16 arrays V, 255-V, V0, 255-V1 stored REVERSED in x
 //                                               (index j = W-1-x); copy c holds element j at position j-c+8, so a
 //                                               run of 8 disparities starting at any j is one aligned LDG.128.
-//   k_cost_h : BT pixel cost for 8 disparities per thread (4 packed registers), running horizontal box sum
-//              along x in registers -> Hs[y][xi][Dp]
-//   k_cost_v : running vertical box sum of Hs -> C, padded disparities overwritten with CPAD
+//   k_cost_fused : BT pixel cost for 8 disparities per cell (4 packed registers), 2R+1 box sum in x through a
+//              shared-memory pix row, running box sum in y through a shared-memory ring -> C (written once),
+//              padded disparities overwritten with CPAD
 //
 // BT in biased form (no negative operands):  with a' = 255-a,
 //   c0+255 = max(255, u+v1', v0+u')   c1+255 = max(255, v+u1', u0+v')   cost = max(min(X,Y)-255, 0)
 //   X = max(u+v1', v0+u'), Y = max(v+u1', u0+v')            -> 2 VIADD + 2 VIADDMNMX + 1 VIMNMX + 1 VIADDMNMX.RELU
 #include "svb_common.cuh"
+#include <algorithm>
 
-#define COST_TXR 32   // x positions per running-sum run
 
 __device__ __forceinline__ int grad_at(const uint8_t *rc, const uint8_t *rn, const uint8_t *rs, int x, int W, int C,
                                        int ch, int ftzero)
@@ -132,162 +132,224 @@ int svb_launch_planes(const SgbmPlan &pl, const uint8_t *left, const uint8_t *ri
     return SVB_OK;
 }
 
-// pixel cost for 8 disparities (4 packed regs) at cost column xc of row y
+// ---- fused cost kernel: BT pixel cost -> horizontal box sum -> vertical running box sum -> C ----
+// One CTA owns a tile of TX = TXP-2R output columns x all disparities and marches down a segment of rows.
+// Per input row r (clamped to the image: cost-space border replication):
+//   phase 1 (window-mapped): the right-image operands of a cell (column xc, disparities 8l..8l+7) are the 8 reversed
+//            pixels starting at w = jb0 - xc + 8l, so all cells on the diagonal xc - 8l = const share them.  A thread
+//            owns one window w: it loads the 4 operand arrays x NPL planes once (aligned LDG.128 from copy w%8,
+//            prefetched one row ahead) and computes every cell of its diagonal inside the tile (<= TXP/8+1 cells),
+//            parking the pixel costs in a double-buffered shared-memory row (column stride Dp+8: conflict-free).
+//   phase 2 (column-mapped): lane l of column block cb walks CPB adjacent output columns with a running sum of the
+//            2R+1 neighbouring pix columns (Hs), swaps Hs into the cell's private slot of a (2R+1)-row ring in
+//            shared memory and updates the vertical running sum acc += Hs(r) - Hs(r-(2R+1)); from the (2R+1)-th
+//            row on it writes C[r-R][x][8l..8l+8).
+// The horizontal sums never touch HBM; C is written exactly once (2 B per pixel-disparity).
+#define COST_THREADS 352
+#define COST_CPB_MAX 6   // output columns per thread (phase 2)
+
 template <int NPL>
-__device__ __forceinline__ void pix8(const uint4 *__restrict__ LProw, const int16_t *__restrict__ RProw, int W1, int Wr8,
-                                     int xc, int jb0, int lane8, uint32_t (&acc)[4])
+struct CostWindow { uint4 v[NPL][4]; };   // [plane][V, 255-V, V0, 255-V1]
+
+template <int NPL>
+__device__ __forceinline__ void load_window(CostWindow<NPL> &cw, const int16_t *__restrict__ RProw, int Wr8, int w)
 {
-    // reversed right index of disparity 0 of this lane: jb = (W-1-x+minD) with x = xc+minX1  ->  jb0 - xc
-    const int j0 = jb0 - xc + lane8;
-    const int cpy = j0 & 7;                       // copy whose position of j0 is 16-byte aligned
-    const int16_t *rb = RProw + (size_t)cpy * 4 * Wr8 + (j0 - cpy + 8);
+    const int cpy = w & 7;
+    const int16_t *rb = RProw + (size_t)cpy * 4 * Wr8 + (w - cpy + 8);
+#pragma unroll
+    for (int pl = 0; pl < NPL; pl++)
+#pragma unroll
+        for (int a = 0; a < 4; a++)
+            cw.v[pl][a] = __ldg(reinterpret_cast<const uint4 *>(rb + ((size_t)pl * 32 + a) * Wr8));
+}
+
+__device__ __forceinline__ uint32_t u4get(const uint4 &q, int i) { return i == 0 ? q.x : i == 1 ? q.y : i == 2 ? q.z : q.w; }
+
+template <int NPL>
+__device__ __forceinline__ void pix_cell(const CostWindow<NPL> &cw, const uint4 *__restrict__ LPx, int W1, uint32_t (&acc)[4])
+{
 #pragma unroll
     for (int i = 0; i < 4; i++) acc[i] = 0;
 #pragma unroll
     for (int pl = 0; pl < NPL; pl++) {
-        const uint4 Lw = __ldg(LProw + (size_t)pl * W1 + xc);
-        const int16_t *rp = rb + (size_t)pl * 32 * Wr8;
-        const uint4 V = __ldg(reinterpret_cast<const uint4 *>(rp));
-        const uint4 Vn = __ldg(reinterpret_cast<const uint4 *>(rp + Wr8));
-        const uint4 V0 = __ldg(reinterpret_cast<const uint4 *>(rp + 2 * Wr8));
-        const uint4 V1n = __ldg(reinterpret_cast<const uint4 *>(rp + 3 * Wr8));
-        const uint32_t v[4] = {V.x, V.y, V.z, V.w}, vn[4] = {Vn.x, Vn.y, Vn.z, Vn.w};
-        const uint32_t v0[4] = {V0.x, V0.y, V0.z, V0.w}, v1n[4] = {V1n.x, V1n.y, V1n.z, V1n.w};
+        const uint4 Lw = __ldg(LPx + (size_t)pl * W1);
 #pragma unroll
         for (int i = 0; i < 4; i++) {
-            const uint32_t Bv = __vadd2(v0[i], Lw.y);                 // v0 + (255-u)
-            const uint32_t X = __viaddmax_s16x2(Lw.x, v1n[i], Bv);    // max(u + 255-v1, .)
-            const uint32_t Ev = __vadd2(Lw.z, vn[i]);                 // u0 + (255-v)
-            const uint32_t Y = __viaddmax_s16x2(v[i], Lw.w, Ev);      // max(v + 255-u1, .)
-            uint32_t c = __viaddmax_s16x2_relu(__vmins2(X, Y), 0xFF01FF01u, 0u);   // max(min-255, 0)
+            const uint32_t Bv = __vadd2(u4get(cw.v[pl][2], i), Lw.y);                 // v0 + (255-u)
+            const uint32_t X = __viaddmax_s16x2(Lw.x, u4get(cw.v[pl][3], i), Bv);     // max(u + 255-v1, .)
+            const uint32_t Ev = __vadd2(Lw.z, u4get(cw.v[pl][1], i));                 // u0 + (255-v)
+            const uint32_t Y = __viaddmax_s16x2(u4get(cw.v[pl][0], i), Lw.w, Ev);     // max(v + 255-u1, .)
+            uint32_t c = __viaddmax_s16x2_relu(__vmins2(X, Y), 0xFF01FF01u, 0u);      // max(min-255, 0)
             if (pl & 1) c = (c >> 2) & 0x3FFF3FFFu;
             acc[i] = __vadd2(acc[i], c);
         }
     }
 }
 
-// grid: (ceil(W1/TXC), H, B); block: 256 threads = G lanes x NRUN runs; run = COST_TXR consecutive columns
 template <int NPL, int R>
-__global__ void __launch_bounds__(256) k_cost_h(const uint4 *__restrict__ LP, const int16_t *__restrict__ RP,
-                                                int16_t *__restrict__ Hs, int H, int W1, int Wr, int Dp, int G, int jb0,
-                                                size_t ws_stride)
+__global__ void __launch_bounds__(COST_THREADS) k_cost_fused(const uint4 *__restrict__ LP, const int16_t *__restrict__ RP,
+                                                             int16_t *__restrict__ Cv, int H, int W1, int Wr, int Dp,
+                                                             int D, int G, int jb0, int TXP, int rows_per_seg,
+                                                             uint32_t cpad, size_t ws_stride)
 {
     constexpr int BS = 2 * R + 1;
-    const int y = blockIdx.y, b = blockIdx.z;
-    const int lane = threadIdx.x % G, run = threadIdx.x / G;
-    const int nrun = 256 / G;
-    const int xa = (blockIdx.x * nrun + run) * COST_TXR;
-    if (xa >= W1) return;
-    const int xe = min(xa + COST_TXR, W1);
+    extern __shared__ __align__(16) unsigned char csm[];
+    const int TX = TXP - 2 * R;
+    const int PS = Dp + 8;                                                 // pix column stride (elements)
+    int16_t *pixbuf = reinterpret_cast<int16_t *>(csm);                    // [2][TXP][PS]
+    int16_t *ring = pixbuf + (size_t)2 * TXP * PS;                         // [BS][TX][Dp]
+    const int b = blockIdx.z, tid = threadIdx.x;
+    const int x0 = blockIdx.x * TX;
+    const int ya = blockIdx.y * rows_per_seg, yb = min(ya + rows_per_seg, H);
+    const int Wr8 = Wr + 8;
     LP = reinterpret_cast<const uint4 *>(reinterpret_cast<const char *>(LP) + (size_t)b * ws_stride);
     RP = reinterpret_cast<const int16_t *>(reinterpret_cast<const char *>(RP) + (size_t)b * ws_stride);
-    Hs = reinterpret_cast<int16_t *>(reinterpret_cast<char *>(Hs) + (size_t)b * ws_stride);
-    const uint4 *LProw = LP + (size_t)y * NPL * W1;
-    const int Wr8 = Wr + 8;
-    const int16_t *RProw = RP + (size_t)y * NPL * 32 * Wr8;
-    uint4 *out = reinterpret_cast<uint4 *>(Hs + ((size_t)y * W1) * Dp + lane * 8);
-    const size_t ostride = Dp / 8;   // uint4 per column
-    uint32_t ring[BS][4];
-    uint32_t sum[4] = {0, 0, 0, 0};
-#pragma unroll
-    for (int i = 0; i < BS; i++)
-#pragma unroll
-        for (int k = 0; k < 4; k++) ring[i][k] = 0;
-    for (int k0 = xa - R; k0 < xe + R; k0 += BS) {
-#pragma unroll
-        for (int i = 0; i < BS; i++) {
-            const int k = k0 + i;
-            const int xc = max(0, min(W1 - 1, k));
-            uint32_t p[4];
-            pix8<NPL>(LProw, RProw, W1, Wr8, xc, jb0, lane * 8, p);
-#pragma unroll
-            for (int q = 0; q < 4; q++) {
-                sum[q] = sum[q] + p[q] - ring[i][q];   // per-half: no carry/borrow (sum>=ring, totals < 2^15)
-                ring[i][q] = p[q];
-            }
-            const int xo = k - R;
-            if (xo >= xa && xo < xe) out[(size_t)xo * ostride] = make_uint4(sum[0], sum[1], sum[2], sum[3]);
-        }
+    Cv = reinterpret_cast<int16_t *>(reinterpret_cast<char *>(Cv) + (size_t)b * ws_stride);
+    {   // ring starts at zero: "subtract the row that leaves the window" is then unconditional
+        uint4 *rz = reinterpret_cast<uint4 *>(ring);
+        const int n = BS * TX * Dp / 8;
+        for (int i = tid; i < n; i += COST_THREADS) rz[i] = make_uint4(0, 0, 0, 0);
     }
-}
-
-// vertical running sum; thread = (column xi, 8 disparities); band of TY rows per CTA in y
-#define COST_TY 40
-template <int R>
-__global__ void __launch_bounds__(256) k_cost_v(const int16_t *__restrict__ Hs, int16_t *__restrict__ Cv, int H, int W1,
-                                                int Dp, int D, uint32_t cpad, size_t ws_stride)
-{
-    const int b = blockIdx.z;
-    const size_t rowq = (size_t)W1 * Dp / 8;   // uint4 per row
-    const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= rowq) return;
-    const uint4 *in = reinterpret_cast<const uint4 *>(reinterpret_cast<const char *>(Hs) + (size_t)b * ws_stride) + t;
-    uint4 *out = reinterpret_cast<uint4 *>(reinterpret_cast<char *>(Cv) + (size_t)b * ws_stride) + t;
-    const int d0 = (int)(t % (Dp / 8)) * 8;
+    // ---- phase-1 role: window w = wmin + tid; valid pix columns of the tile are [xlo, xhi] ----
+    const int xlo = max(x0 - R, 0), xhi = min(x0 - R + TXP - 1, W1 - 1);
+    const int w = jb0 - xhi + tid;
+    const bool hasWin = tid < (xhi - xlo) + 8 * (G - 1) + 1;
+    // cells of this window: xc = jb0 - w + 8l in [xlo, xhi], l in [0, G)
+    const int xb = jb0 - w;                                 // column of l = 0 (<= xhi)
+    const int l_lo = max(0, (xlo - xb + 7) >> 3), l_hi = hasWin ? min(G - 1, (xhi - xb) >> 3) : -1;
+    // ---- phase-2 role: lane l of column block cb ----
+    const int lane = tid % G, cb = tid / G, NCB = COST_THREADS / G;
+    const int CPB = (TX + NCB - 1) / NCB;
+    const int c0 = cb * CPB;                                // first output column (tile-local) of this thread
     uint32_t keep[4];
 #pragma unroll
     for (int k = 0; k < 4; k++)
-        keep[k] = ((d0 + 2 * k < D) ? 0x0000FFFFu : 0u) | ((d0 + 2 * k + 1 < D) ? 0xFFFF0000u : 0u);
-    const int y0 = blockIdx.y * COST_TY, y1 = min(y0 + COST_TY, H);
-    uint32_t v[4] = {0, 0, 0, 0};
+        keep[k] = ((lane * 8 + 2 * k < D) ? 0x0000FFFFu : 0u) | ((lane * 8 + 2 * k + 1 < D) ? 0xFFFF0000u : 0u);
+    uint32_t acc[COST_CPB_MAX][4];
 #pragma unroll
-    for (int dy = -R; dy <= R; dy++) {
-        const uint4 a = __ldg(in + (size_t)max(0, min(H - 1, y0 + dy)) * rowq);
-        v[0] += a.x; v[1] += a.y; v[2] += a.z; v[3] += a.w;
-    }
-    for (int y = y0; y < y1; y++) {
-        uint4 o;
-        o.x = (v[0] & keep[0]) | (cpad & ~keep[0]);
-        o.y = (v[1] & keep[1]) | (cpad & ~keep[1]);
-        o.z = (v[2] & keep[2]) | (cpad & ~keep[2]);
-        o.w = (v[3] & keep[3]) | (cpad & ~keep[3]);
-        out[(size_t)y * rowq] = o;
-        const uint4 a = __ldg(in + (size_t)min(H - 1, y + R + 1) * rowq);
-        const uint4 s = __ldg(in + (size_t)max(0, y - R) * rowq);
-        v[0] = v[0] + a.x - s.x; v[1] = v[1] + a.y - s.y; v[2] = v[2] + a.z - s.z; v[3] = v[3] + a.w - s.w;
+    for (int k = 0; k < COST_CPB_MAX; k++)
+#pragma unroll
+        for (int q = 0; q < 4; q++) acc[k][q] = 0;
+    int slot = 0;
+    const int r0 = ya - R, r1 = yb - 1 + R;
+    CostWindow<NPL> cur, nxt;
+    if (hasWin) load_window<NPL>(cur, RP + (size_t)max(0, min(H - 1, r0)) * NPL * 32 * Wr8, Wr8, w);
+    for (int r = r0; r <= r1; r++) {
+        const int rc = max(0, min(H - 1, r));
+        int16_t *pb = pixbuf + (size_t)((r - r0) & 1) * TXP * PS;
+        // ---- phase 1 ----
+        {
+            const uint4 *LProw = LP + (size_t)rc * NPL * W1;
+            for (int l = l_lo; l <= l_hi; l++) {
+                const int xc = xb + 8 * l;
+                uint32_t p[4];
+                pix_cell<NPL>(cur, LProw + xc, W1, p);
+                *reinterpret_cast<uint4 *>(pb + (size_t)(xc - (x0 - R)) * PS + l * 8) = make_uint4(p[0], p[1], p[2], p[3]);
+            }
+            if (hasWin && r < r1) load_window<NPL>(nxt, RP + (size_t)max(0, min(H - 1, r + 1)) * NPL * 32 * Wr8, Wr8, w);
+        }
+        __syncthreads();
+        // ---- phase 2 ----
+        const bool emit = r >= ya + R;
+        const int y = r - R;
+        if (c0 < TX && x0 + c0 < W1) {
+            // pix column of output column c, offset dx: tile-local index c+dx, clamped to the valid columns
+            auto pixcol = [&](int ci) -> const int16_t * {
+                const int x = max(xlo, min(xhi, x0 - R + ci));
+                return pb + (size_t)(x - (x0 - R)) * PS + lane * 8;
+            };
+            uint32_t hs[4] = {0, 0, 0, 0};
+#pragma unroll
+            for (int dx = 0; dx < BS; dx++) {
+                const uint4 v = *reinterpret_cast<const uint4 *>(pixcol(c0 + dx));
+                hs[0] += v.x; hs[1] += v.y; hs[2] += v.z; hs[3] += v.w;   // per-half sums < 2^15: no carry
+            }
+#pragma unroll
+            for (int k = 0; k < COST_CPB_MAX; k++) {
+                const int c = c0 + k;
+                if (k < CPB && c < TX && x0 + c < W1) {
+                    if (k > 0) {   // slide the window one column to the right
+                        const uint4 vin = *reinterpret_cast<const uint4 *>(pixcol(c + BS - 1));
+                        const uint4 vout = *reinterpret_cast<const uint4 *>(pixcol(c - 1));
+                        hs[0] += vin.x - vout.x; hs[1] += vin.y - vout.y; hs[2] += vin.z - vout.z; hs[3] += vin.w - vout.w;
+                    }
+                    uint4 *cell = reinterpret_cast<uint4 *>(ring + ((size_t)slot * TX + c) * Dp + lane * 8);
+                    const uint4 old = *cell;
+                    *cell = make_uint4(hs[0], hs[1], hs[2], hs[3]);
+                    acc[k][0] += hs[0] - old.x; acc[k][1] += hs[1] - old.y;
+                    acc[k][2] += hs[2] - old.z; acc[k][3] += hs[3] - old.w;     // acc >= old per half: no borrow
+                    if (emit) {
+                        uint4 o;
+                        o.x = (acc[k][0] & keep[0]) | (cpad & ~keep[0]);
+                        o.y = (acc[k][1] & keep[1]) | (cpad & ~keep[1]);
+                        o.z = (acc[k][2] & keep[2]) | (cpad & ~keep[2]);
+                        o.w = (acc[k][3] & keep[3]) | (cpad & ~keep[3]);
+                        *reinterpret_cast<uint4 *>(Cv + ((size_t)y * W1 + x0 + c) * Dp + lane * 8) = o;
+                    }
+                }
+            }
+        }
+        slot = slot + 1 == BS ? 0 : slot + 1;
+        cur = nxt;
     }
 }
 
-template <int NPL>
-static void launch_cost_h(int R, dim3 grid, cudaStream_t st, const uint4 *LP, const int16_t *RP, int16_t *Hs, int H,
-                          int W1, int Wr, int Dp, int G, int jb0, size_t ws_stride)
+struct CostGeom { int TXP, TX, ntiles, rows_per_seg, nseg; size_t smem; };
+static CostGeom cost_geom(const SgbmPlan &pl)
 {
-    switch (R) {
-    case 0: k_cost_h<NPL, 0><<<grid, 256, 0, st>>>(LP, RP, Hs, H, W1, Wr, Dp, G, jb0, ws_stride); break;
-    case 1: k_cost_h<NPL, 1><<<grid, 256, 0, st>>>(LP, RP, Hs, H, W1, Wr, Dp, G, jb0, ws_stride); break;
-    case 2: k_cost_h<NPL, 2><<<grid, 256, 0, st>>>(LP, RP, Hs, H, W1, Wr, Dp, G, jb0, ws_stride); break;
-    case 3: k_cost_h<NPL, 3><<<grid, 256, 0, st>>>(LP, RP, Hs, H, W1, Wr, Dp, G, jb0, ws_stride); break;
-    case 4: k_cost_h<NPL, 4><<<grid, 256, 0, st>>>(LP, RP, Hs, H, W1, Wr, Dp, G, jb0, ws_stride); break;
-    default: k_cost_h<NPL, 5><<<grid, 256, 0, st>>>(LP, RP, Hs, H, W1, Wr, Dp, G, jb0, ws_stride); break;
+    CostGeom g;
+    const int Gc = pl.Dp / 8, NCB = COST_THREADS / Gc, BS = 2 * pl.R + 1;
+    const size_t budget = 200 * 1024;
+    auto bytes = [&](int txp) { return (size_t)2 * ((size_t)2 * txp * (pl.Dp + 8) + (size_t)BS * (txp - 2 * pl.R) * pl.Dp); };
+    // widest tile whose windows fit the CTA (TXP + 8(G-1) <= threads), whose column blocks fit COST_CPB_MAX and
+    // whose buffers fit shared memory
+    int TXP = std::min(COST_THREADS - 8 * (Gc - 1), NCB * COST_CPB_MAX + 2 * pl.R);
+    TXP = std::min(TXP, pl.W1 + 2 * pl.R);
+    while (TXP > 2 * pl.R + 1 && bytes(TXP) > budget) TXP--;
+    g.TXP = TXP; g.TX = TXP - 2 * pl.R;
+    g.ntiles = (pl.W1 + g.TX - 1) / g.TX;
+    g.nseg = std::max(1, std::min(8, pl.H / 32));
+    g.rows_per_seg = (pl.H + g.nseg - 1) / g.nseg;
+    g.nseg = (pl.H + g.rows_per_seg - 1) / g.rows_per_seg;
+    g.smem = bytes(TXP);
+    return g;
+}
+
+template <int NPL, int R>
+static int launch_cost_fused(const SgbmPlan &pl, const CostGeom &g, char *ws, size_t ws_stride, int B, cudaStream_t st)
+{
+    auto kern = k_cost_fused<NPL, R>;
+    static size_t configured = 0;
+    if (g.smem > configured) {
+        SVB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g.smem));
+        configured = g.smem;
+    }
+    const int jb0 = pl.W - 1 - pl.minX1 + pl.p.minDisparity;
+    const uint32_t cpad = (uint32_t)(32767 - pl.p.P2) * 0x10001u;
+    dim3 grid(g.ntiles, g.nseg, B);
+    kern<<<grid, COST_THREADS, g.smem, st>>>((const uint4 *)(ws + pl.off_lplanes), (const int16_t *)(ws + pl.off_rplanes),
+                                             (int16_t *)(ws + pl.off_C), pl.H, pl.W1, pl.Wr, pl.Dp, pl.D, pl.Dp / 8, jb0,
+                                             g.TXP, g.rows_per_seg, cpad, ws_stride);
+    SVB_CUDA_CHECK(cudaGetLastError());
+    return SVB_OK;
+}
+
+template <int NPL>
+static int launch_cost_r(const SgbmPlan &pl, const CostGeom &g, char *ws, size_t ws_stride, int B, cudaStream_t st)
+{
+    switch (pl.R) {
+    case 0: return launch_cost_fused<NPL, 0>(pl, g, ws, ws_stride, B, st);
+    case 1: return launch_cost_fused<NPL, 1>(pl, g, ws, ws_stride, B, st);
+    case 2: return launch_cost_fused<NPL, 2>(pl, g, ws, ws_stride, B, st);
+    case 3: return launch_cost_fused<NPL, 3>(pl, g, ws, ws_stride, B, st);
+    case 4: return launch_cost_fused<NPL, 4>(pl, g, ws, ws_stride, B, st);
+    default: return launch_cost_fused<NPL, 5>(pl, g, ws, ws_stride, B, st);
     }
 }
 
 int svb_launch_cost(const SgbmPlan &pl, char *ws, size_t ws_stride, int B, cudaStream_t st)
 {
-    const uint4 *LP = (const uint4 *)(ws + pl.off_lplanes);
-    const int16_t *RP = (const int16_t *)(ws + pl.off_rplanes);
-    int16_t *Hs = (int16_t *)(ws + pl.off_S);   // S volume doubles as the horizontal-sum scratch
-    int16_t *Cv = (int16_t *)(ws + pl.off_C);
-    const int Gc = pl.Dp / 8;   // cost threads hold 8 disparities each
-    const int nrun = 256 / Gc;
-    const int jb0 = pl.W - 1 - pl.minX1 + pl.p.minDisparity;
-    dim3 grid((pl.W1 + nrun * COST_TXR - 1) / (nrun * COST_TXR), pl.H, B);
-    if (pl.nplanes == 2)
-        launch_cost_h<2>(pl.R, grid, st, LP, RP, Hs, pl.H, pl.W1, pl.Wr, pl.Dp, Gc, jb0, ws_stride);
-    else
-        launch_cost_h<6>(pl.R, grid, st, LP, RP, Hs, pl.H, pl.W1, pl.Wr, pl.Dp, Gc, jb0, ws_stride);
-    SVB_CUDA_CHECK(cudaGetLastError());
-    const size_t rowq = (size_t)pl.W1 * pl.Dp / 8;
-    dim3 g2((unsigned)((rowq + 255) / 256), (pl.H + COST_TY - 1) / COST_TY, B);
-    const uint32_t cpad = (uint32_t)(32767 - pl.p.P2) * 0x10001u;
-    switch (pl.R) {
-    case 0: k_cost_v<0><<<g2, 256, 0, st>>>(Hs, Cv, pl.H, pl.W1, pl.Dp, pl.D, cpad, ws_stride); break;
-    case 1: k_cost_v<1><<<g2, 256, 0, st>>>(Hs, Cv, pl.H, pl.W1, pl.Dp, pl.D, cpad, ws_stride); break;
-    case 2: k_cost_v<2><<<g2, 256, 0, st>>>(Hs, Cv, pl.H, pl.W1, pl.Dp, pl.D, cpad, ws_stride); break;
-    case 3: k_cost_v<3><<<g2, 256, 0, st>>>(Hs, Cv, pl.H, pl.W1, pl.Dp, pl.D, cpad, ws_stride); break;
-    case 4: k_cost_v<4><<<g2, 256, 0, st>>>(Hs, Cv, pl.H, pl.W1, pl.Dp, pl.D, cpad, ws_stride); break;
-    default: k_cost_v<5><<<g2, 256, 0, st>>>(Hs, Cv, pl.H, pl.W1, pl.Dp, pl.D, cpad, ws_stride); break;
-    }
-    SVB_CUDA_CHECK(cudaGetLastError());
-    return SVB_OK;
+    const CostGeom g = cost_geom(pl);
+    SVB_REQUIRE(g.smem <= 227 * 1024, SVB_ERR_UNSUPPORTED, "sgbm: cost tile does not fit shared memory (%zu bytes)", g.smem);
+    return pl.nplanes == 2 ? launch_cost_r<2>(pl, g, ws, ws_stride, B, st) : launch_cost_r<6>(pl, g, ws, ws_stride, B, st);
 }
