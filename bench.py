@@ -39,6 +39,17 @@ def _peaks():
         return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
+def _ncu_traffic(B: int):
+    """dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel from the committed ncu --set full capture
+    (profiles/r01_traffic.json, per launch at the batch it was captured with; scaled linearly to this batch)."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "r01_traffic.json")) as f:
+            t = json.load(f)["k_sweep_pass2"]
+        return float(t["dram_bytes"]) * B / t["batch"], "%s (B=%d, scaled x%g)" % (t["source"], t["batch"], B / t["batch"])
+    except Exception:
+        return None, "no capture committed"
+
+
 class ClockSampler:
     """Samples nvidia-smi clocks / throttle reasons during the timed region."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
@@ -250,7 +261,11 @@ def run_ours(args):
     alg_bytes = 4.0 * W1 * H * Dp * B                      # 2 B of C + 2 B of S per (pixel, disparity)
     peak, peak_src = _peaks()
     ach = alg_bytes / (stage_ms[dom] / 1e3) / 1e9
-    ops16 = 9.0 * W1 * H * D * 4 * B                        # 9 16-bit ops per (px, d, path), 4 paths/pass
+    # 9 16-bit ops per (px, d, path); 4 paths per pass, 8 per frame pair (MODE_HH)
+    ops16_pass = 9.0 * W1 * H * D * 4 * B
+    agg_ms = stage_ms["aggregate_pass1"] + stage_ms[dom]
+    alu = sv.packed_alu_peak(local)
+    traffic, traffic_src = _ncu_traffic(B)
     cores = os.cpu_count() or 1
     cpu_v, cpu_kind, cpu_c, cpu_desc = cpu_reference_fps(max(1, min(cores, 32))) if not args.no_cpu else (None, "skipped", 0, "")
     line = {
@@ -262,14 +277,21 @@ def run_ours(args):
                    "l2": "per-step working set (C+S volumes, %.1f GB/GPU) >> 126 MB L2; no explicit flush" % (2 * 2.0 * W1 * H * Dp * B / 1e9)},
         "e2e": {"value": fps_e2e, "unit": "frames/s", "h2d_bytes_per_step": int(2 * B * H * W),
                 "d2h_bytes_per_step": int(B * H * W * 2 + B * NBOX * 4), "gpix_disp_per_s": fps_e2e * W * H * D / 1e9},
-        "gpu_launches": 12 * args.steps,
+        "gpu_launches": 11 * args.steps,   # planes, cost, sweep x2, lrcheck, median3, ccl x4, box_median
         "clocks": clocks,
         "stage_ms_per_step": stage_ms,
-        "roofline": {"kernel": "k_sweep<NR=4,G=32,NV=3,PASS2> (aggregation pass 2 + selection)", "bound": "hbm",
-                     "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
+        "roofline": {"kernel": "k_sweep<NR=4,G=32,NGRP=15,NV=3,PASS2> (aggregation pass 2 + selection)", "bound": "hbm",
+                     "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": traffic,
+                     "traffic_source": traffic_src,
                      "peak_source": peak_src, "algorithmic_bytes_per_launch": alg_bytes,
                      "share_of_step": stage_ms[dom] / sum(stage_ms.values()),
-                     "alu_ops16_per_s": ops16 / (stage_ms[dom] / 1e3)},
+                     "note": "this kernel is packed-int ALU-bound by design (north_star); see alu_roofline"},
+        # north_star's aggregation roofline: algorithmic 16-bit ops (9 per px*d*path) against the packed-int ALU peak
+        # measured live by svb_measure_packed_alu_peak (VIADDMNMX/VIMNMX.S16x2 chains on all SMs, x2 lanes)
+        "alu_roofline": {"stage": "aggregation (both sweeps)", "achieved_ops16_per_s": 2 * ops16_pass / (agg_ms / 1e3),
+                         "peak_ops16_per_s": alu["ops16_per_s"], "frac": 2 * ops16_pass / (agg_ms / 1e3) / alu["ops16_per_s"],
+                         "pass2_only_frac": ops16_pass / (stage_ms[dom] / 1e3) / alu["ops16_per_s"],
+                         "peak_source": "measured live (svb_measure_packed_alu_peak)"},
         "cpu_baseline": {"value": cpu_v, "unit": "frames/s", "cores": cpu_c, "kind": cpu_kind, "sample": cpu_desc},
     }
     print(json.dumps(line), flush=True)

@@ -120,6 +120,11 @@ int svb_box_median_depth(svb_context *ctx, const int16_t *disp16, int H, int W, 
                          const double *Q, int invalid16, const float *boxes, const int32_t *box_image, int nboxes,
                          float *out, void *stream);
 
+/* ---- measurement helper (bench.py): device peak of packed s16x2 ALU instructions (VIADDMNMX / VIMNMX chains on
+ * all SMs), in thread-level packed instructions per second; x2 = 16-bit lane operations per second.  This is the
+ * roofline denominator of the aggregation stage. */
+int svb_measure_packed_alu_peak(svb_context *ctx, double *packed_instr_per_s, double *sm_clock_mhz, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -3,7 +3,7 @@ jacksonroah/stereo-vision hot path: rectify -> StereoSGBM -> reprojectImageTo3D 
 from .api import (  # noqa: F401
     BORDER_CONSTANT, CV_16SC2, CV_32FC1, INTER_LINEAR, STEREO_SGBM_MODE_HH, STEREO_SGBM_MODE_HH4,
     STEREO_SGBM_MODE_SGBM, STEREO_SGBM_MODE_SGBM_3WAY, StereoSGBM, StereoSGBM_create, box_median_depth,
-    filterSpeckles, initUndistortRectifyMap, last_stage_ms, medianBlur, release_workspaces, remap,
+    filterSpeckles, initUndistortRectifyMap, last_stage_ms, medianBlur, packed_alu_peak, release_workspaces, remap,
     reprojectImageTo3D, set_stage_timing,
 )
 from ._lib import SvbError  # noqa: F401

@@ -28,7 +28,7 @@ EXPORTS = [
     "svb_last_error", "svb_version", "svb_create", "svb_destroy", "svb_sgbm_resolve_params", "svb_sgbm_get_geometry",
     "svb_sgbm_workspace_bytes", "svb_sgbm_compute", "svb_sgbm_debug_stages", "svb_median3_s16",
     "svb_filter_speckles_s16", "svb_init_undistort_rectify_map", "svb_remap_u8", "svb_reproject_to_3d",
-    "svb_box_median_depth", "svb_set_timing", "svb_sgbm_last_stage_ms",
+    "svb_box_median_depth", "svb_set_timing", "svb_sgbm_last_stage_ms", "svb_measure_packed_alu_peak",
 ]
 
 _lib = None
@@ -61,6 +61,7 @@ def load():
     lib.svb_box_median_depth.argtypes = [vp, vp, i32, i32, sz, vp, i32, vp, vp, i32, vp, vp]
     lib.svb_set_timing.argtypes = [vp, i32]
     lib.svb_sgbm_last_stage_ms.argtypes = [vp, C.POINTER(C.c_float), i32]
+    lib.svb_measure_packed_alu_peak.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_double), vp]
     for n in EXPORTS:
         f = getattr(lib, n)
         if n not in ("svb_last_error", "svb_version"):

@@ -359,3 +359,12 @@ def last_stage_ms(device=None) -> dict:
     ms = (C.c_float * 6)()
     check(_lib.load().svb_sgbm_last_stage_ms(_lib.context(dev), ms, 6))
     return dict(zip(STAGE_NAMES, [float(v) for v in ms]))
+
+
+def packed_alu_peak(device=None) -> dict:
+    """Measured device peak of packed s16x2 ALU instructions (svb_measure_packed_alu_peak): the roofline denominator
+    of the aggregation stage.  Returns packed instructions/s (thread level) and 16-bit lane operations/s (x2)."""
+    dev = torch.cuda.current_device() if device is None else int(device)
+    rate, mhz = C.c_double(), C.c_double()
+    check(_lib.load().svb_measure_packed_alu_peak(_lib.context(dev), C.byref(rate), C.byref(mhz), _stream(dev)))
+    return {"packed_instr_per_s": rate.value, "ops16_per_s": 2.0 * rate.value, "sm_clock_max_mhz": mhz.value}
