@@ -28,10 +28,13 @@
 
 #define AGG_SLOTS 4        // ring depth (u-1, u, u+1 live + one being written)
 #define AGG_ENS 8          // slots of the cross-band "row -1" ring
-#define AGG_EPF 4          // cross-band prefetch distance (pixels)
+#define AGG_EPF 6          // cross-band prefetch distance (pixels); EPF + 2 <= ENS
 #define AGG_PUB 8          // publish cross-band progress every AGG_PUB pixels
 #define AGG_PADE 8         // int16 elements of P2 halo in front of every ring vector
 
+#ifdef EXP_HARNESS
+__device__ unsigned long long g_spin[4];
+#endif
 struct AggArgs {
     const int16_t *C;      // [H][W1][Dp]
     int16_t *S;            // [H][W1][Dp]   pass 1: out, pass 2: in
@@ -46,12 +49,16 @@ struct AggArgs {
     int flip;              // 0: rows top-down, x ascending; 1: both reversed
     uint32_t P1d, P2d;     // duplicated halves
     int uniq, invalid16;
+    int slack;             // extra producer lead a starving band waits for (0 when one frame is in flight)
 };
 
+// Progress poll.  A relaxed (L1-bypassing) load, not ld.acquire: ptxas lowers every gpu-scope acquire/fence to
+// LDG + CCTL.IVALL, i.e. an invalidation of the SM's whole L1 on every poll.  The data the flag guards is only ever
+// read with cp.async.cg (L2, bypasses L1) issued after the loop exit in program order, so no stale line can be hit.
 __device__ __forceinline__ unsigned ld_acquire(const unsigned *p)
 {
     unsigned v;
-    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
     return v;
 }
 __device__ __forceinline__ void st_release(unsigned *p, unsigned v)
@@ -70,6 +77,9 @@ __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_gr
 template <int G>
 __device__ __forceinline__ uint32_t group_min_u32(uint32_t v)
 {
+#ifdef EXP_NOREDUX
+    return v;
+#endif
     if (G == 32) return __reduce_min_sync(0xffffffffu, v);
 #pragma unroll
     for (int o = G >> 1; o; o >>= 1) v = min(v, __shfl_xor_sync(0xffffffffu, v, o));
@@ -293,7 +303,11 @@ struct SweepLane {
         // ---- vertical / diagonal paths: predecessors (u-1, u, u+1) of the previous row ----
         if (NV) {
             int16_t *wbase = act ? ownL : trashL;
+#ifdef EXP_NOEDGEST
+            const bool epred = false;
+#else
             const bool epred = act && edge_out != nullptr;
+#endif
             int16_t *eptr = edge_out + (size_t)(act ? u : 0) * 3 * Dp;
 #pragma unroll
             for (int j = 0; j < 3; j++) {
@@ -358,7 +372,11 @@ struct SweepLane {
     }
 };
 
+#ifdef EXP_NOBAR
+__device__ __forceinline__ void cta_barrier() {}
+#else
 __device__ __forceinline__ void cta_barrier() { asm volatile("bar.sync 0;" ::: "memory"); }
+#endif
 
 // NV = 3: wavefront sweep with the three vertical/diagonal predecessors (+ one DMA warp per CTA);
 // NV = 0: horizontal path only (rows independent; the 5th path of MODE_SGBM), no barriers, no DMA warp.
@@ -414,51 +432,69 @@ __global__ void __launch_bounds__(NGRP *G + (NV ? 32 : 0)) k_sweep(const __grid_
         const bool consumer = band > 0, producer = band + 1 < a.nbands;
         const int16_t *edge_in = edge + (size_t)(consumer ? band - 1 : 0) * edge_band;
         const unsigned *prog_in = prog + (consumer ? band - 1 : 0);
-        const int cpv = Dp / 8;            // 16-byte chunks per vector
-        const int nch = 3 * cpv;
-        unsigned known = 0;
+        constexpr int CPV = G * NR / 4;    // 16-byte chunks per vector (Dp / 8), a power of two
+        constexpr int NCH = 3 * CPV;
         auto fetch = [&](int pe) {         // pixel pe of the producer band's last row -> row -1 ring
+#ifdef EXP_FETCHHOT
+            const int16_t *src = edge_in + (size_t)(pe & 63) * 3 * Dp;
+#else
             const int16_t *src = edge_in + (size_t)pe * 3 * Dp;
+#endif
             int16_t *dst = rowm1 + (size_t)((pe & (AGG_ENS - 1)) * 3) * VS + AGG_PADE;
-            for (int i = lane; i < nch; i += 32) {
-                const int j = i / cpv, k = i - j * cpv;
-                cp_async16(dst + j * VS + k * 8, src + i * 8);
+#ifndef EXP_NOFETCH
+#pragma unroll
+            for (int i0 = 0; i0 < NCH; i0 += 32) {
+                const int i = i0 + lane;
+                if (NCH % 32 == 0 || i < NCH) cp_async16(dst + (i / CPV) * VS + (i % CPV) * 8, src + i * 8);
             }
+#endif
         };
-        auto wait_for = [&](unsigned need) {
-            if (lane == 0)
-                while (known < need) known = ld_acquire(prog_in);
-            __syncwarp();
-        };
-        if (consumer) {
-            const int n0 = min(AGG_EPF, W1);
-            wait_for((unsigned)n0);
-            for (int pe = 0; pe < n0; pe++) fetch(pe);
-        }
-        cp_async_commit();
-        cp_async_wait<0>();
+        // Non-blocking hand-off: the progress counter is re-read every step with the load issued one step before its
+        // value is used; pixels are pulled up to AGG_EPF ahead of row 0 as far as the producer allows (at most two per
+        // step when catching up).  Only when the pixel row 0 needs next is not even published does the warp spin.
+        unsigned known = consumer ? 0u : (unsigned)W1, pending = 0;
+        int fetched = consumer ? 0 : W1;   // pixels [0, fetched) are issued
+        int f1 = fetched, f2 = fetched;    // 'fetched' one and two steps ago
+#ifdef EXP_NOPOLL
+        known = (unsigned)W1;
+#endif
+        if (consumer) pending = ld_acquire(prog_in);
         for (int t = 0; t < nsteps; t++) {
-            const int pe = t + AGG_EPF;
-            if (consumer && pe < W1) {
-                wait_for((unsigned)(pe + 1));
-                fetch(pe);
+            if (consumer) {
+                known = max(known, pending);
+                if (known < (unsigned)W1) pending = ld_acquire(prog_in);
+                const int need = min(t + 2, W1);                       // pixels row 0 reads in step t: < t+2
+#ifdef EXP_HARNESS
+                if ((int)known < need && lane == 0) { atomicAdd(&g_spin[0], 1ull); }
+                { long long c0 = clock64();
+#endif
+                if ((int)known < need) {   // starving: wait until the producer is a.slack pixels further (hysteresis:
+                    const int target = min(need + a.slack, W1);   // equal-speed bands would otherwise re-starve at once)
+                    while ((int)known < target) known = ld_acquire(prog_in);
+                }
+#ifdef EXP_HARNESS
+                  if (lane == 0) atomicAdd(&g_spin[1], (unsigned long long)(clock64() - c0)); }
+                if (lane == 0) atomicAdd(&g_spin[2], 1ull);
+#endif
+                const int limit = min(min(t + 1 + AGG_EPF, W1), (int)known);
+                if (fetched < limit) fetch(fetched++);
+                if (fetched < limit) fetch(fetched++);
             }
             cp_async_commit();
-            cp_async_wait<AGG_EPF - 1>();
+            // everything issued up to two steps ago is complete after wait_group<2>; fall back when that is not enough
+            const int need = min(t + 2, W1);
+            if (f2 >= need) cp_async_wait<2>();
+            else if (f1 >= need) cp_async_wait<1>();
+            else cp_async_wait<0>();
+            f2 = f1; f1 = fetched;
             cta_barrier();
             if (producer && lane == 0) {
                 const int done = t - lag_last;   // pixels of the last row finished before this barrier
-                if (done > 0 && done < W1 && (done % AGG_PUB) == 0) {
-                    __threadfence();
-                    st_release(prog + band, (unsigned)done);
-                }
+                if (done > 0 && done < W1 && (done % AGG_PUB) == 0) st_release(prog + band, (unsigned)done);
             }
         }
         cta_barrier();
-        if (producer && lane == 0) {
-            __threadfence();
-            st_release(prog + band, (unsigned)W1);
-        }
+        if (producer && lane == 0) st_release(prog + band, (unsigned)W1);
         return;
     }
 
@@ -567,6 +603,7 @@ int svb_launch_aggregate(svb_context *ctx, const SgbmPlan &pl, char *ws, size_t 
     a.P2d = (uint32_t)pl.p.P2 * 0x10001u;
     a.uniq = pl.p.uniquenessRatio;
     a.invalid16 = pl.invalid16;
+    a.slack = B > 1 ? 16 : 0;
     const int pad = pl.Dp != pl.D;
     const int NR = pl.E / 2;
     // pass 1: left, up-left, up, up-right

@@ -1,0 +1,46 @@
+// Timing harness for k_sweep variants (single-band frames: no cross-band coupling).  Not part of the product.
+// Stubs for the host-side helpers svb_aggregate.cu references:
+#include "../stereo_vision_b200/csrc/svb_aggregate.cu"
+#include <vector>
+void svb_set_error(const char *, ...) {}
+int main(int argc, char **argv)
+{
+    const int H = argc > 2 ? atoi(argv[2]) : 15, W1 = 1664, Dp = 256, B = argc > 1 ? atoi(argv[1]) : 148, W = 1920;
+    const int NB = (H + 14) / 15;
+    const size_t vol = (size_t)H * W1 * Dp * 2, edge = (size_t)NB * W1 * 3 * Dp * 2;
+    const size_t stride = ((2 * vol + edge + 4096 + (size_t)H * W * 6) + 255) / 256 * 256 + 256;
+    char *ws; cudaMalloc(&ws, stride * B + (1 << 20));
+    ws += 1 << 19;   // margin in front (unclamped prefetch experiments)
+    std::vector<int16_t> h(vol / 2);
+    if (cudaGetLastError() != cudaSuccess) { printf("alloc failed\n"); return 1; }
+    for (size_t i = 0; i < h.size(); i++) h[i] = (int16_t)((i * 2654435761u >> 20) % 3000);
+    cudaMemcpy(ws, h.data(), vol, cudaMemcpyHostToDevice);
+    for (int b = 1; b < B; b++) cudaMemcpy(ws + b * stride, ws, vol, cudaMemcpyDeviceToDevice);
+    unsigned *tick; cudaMalloc(&tick, 64);
+    AggArgs a; memset(&a, 0, sizeof a);
+    a.C = (int16_t *)ws; a.S = (int16_t *)(ws + vol); a.edge = (int16_t *)(ws + 2 * vol);
+    a.prog = (unsigned *)(ws + 2 * vol + edge); a.dpre = (int16_t *)(ws + 2 * vol + edge + 4096);
+    a.keys = (unsigned *)(ws + 2 * vol + edge + 4096 + (size_t)H * W * 2);
+    a.ws_stride = (argc > 4 && atoi(argv[4])) ? 0 : stride;   // hot: every frame aliases frame 0 (L2-resident) a.H = H; a.W = W; a.W1 = W1; a.D = 256; a.Dp = Dp; a.minX1 = 256; a.minD = 0;
+    a.nbands = NB; a.B = B; a.P1d = 200 * 0x10001u; a.P2d = 800 * 0x10001u; a.uniq = 10; a.invalid16 = -16; a.slack = argc > 3 ? atoi(argv[3]) : 0;
+    cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
+    for (int pass = 0; pass < 2; pass++) {
+        float best = 1e9;
+        for (int rep = 0; rep < 4; rep++) {
+            cudaMemset(tick, 0, 64);
+            for (int b = 0; b < B; b++) cudaMemset(ws + b * stride + 2 * vol + edge, 0, 4096);
+            a.ticket = tick; a.flip = pass; a.prog = (unsigned *)(ws + 2 * vol + edge) + pass * 512;
+            cudaEventRecord(e0);
+            if (pass == 0) launch_sweep_t<4, 32, 15, 3, false, true, false>(a, B * NB, 0);
+            else launch_sweep_t<4, 32, 15, 3, true, true, false>(a, B * NB, 0);
+            cudaEventRecord(e1); cudaEventSynchronize(e1);
+            float ms; cudaEventElapsedTime(&ms, e0, e1); if (ms < best) best = ms;
+        }
+        unsigned long long sp[4]; cudaMemcpyFromSymbol(sp, g_spin, sizeof sp); unsigned long long z[4] = {0,0,0,0}; cudaMemcpyToSymbol(g_spin, z, sizeof z);
+        printf("   starved steps %.2f%% of consumer steps, spin cycles per consumer step %.1f\n", 100.0 * sp[0] / (sp[2] + 1), (double)sp[1] / (sp[2] + 1));
+        cudaError_t e = cudaGetLastError();
+        const double steps = 1696.0 * B * NB / 148.0;
+        printf("pass%d B=%d: %.3f ms  -> %.0f cycles/step @1.965GHz  (%s)\n", pass + 1, B, best, best * 1e-3 / steps * 1.965e9, cudaGetErrorString(e));
+    }
+    return 0;
+}
