@@ -28,7 +28,8 @@
 
 #define AGG_SLOTS 4        // ring depth (u-1, u, u+1 live + one being written)
 #define AGG_ENS 8          // slots of the cross-band "row -1" ring
-#define AGG_EPF 6          // cross-band prefetch distance (pixels); EPF + 2 <= ENS
+#define AGG_EPF 5          // cross-band prefetch distance: at step t pixels <= t+EPF may be issued; the slot of pixel
+                           // t+EPF holds pixel t+EPF-ENS, which row 0 may still be reading in step t-1 unless EPF <= ENS-3
 #define AGG_PUB 8          // publish cross-band progress every AGG_PUB pixels
 #define AGG_PADE 8         // int16 elements of P2 halo in front of every ring vector
 

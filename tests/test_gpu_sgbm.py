@@ -108,3 +108,19 @@ def test_error_behaviour(sv):
     v = big[::2, ::1]
     assert np.array_equal(m.compute(v, v), oracle.sgbm_compute(np.ascontiguousarray(v), np.ascontiguousarray(v),
                                                                 numDisparities=64, blockSize=5))
+
+
+@pytest.mark.parametrize("name,B", [("c3", 6), ("c5", 2)])
+def test_full_size_batch_is_race_free(sv, golden_full, name, B):
+    """A batch of identical full-size pairs keeps many bands of several frames in flight at once (cross-band hand-off,
+    ticket scheduling, edge prefetch): every frame must still hash to the cv2 golden, twice in a row."""
+    import torch
+    L, R, kw = cases.full_inputs(name)
+    Lb = torch.from_numpy(L).cuda()[None].repeat(B, 1, 1).contiguous()
+    Rb = torch.from_numpy(R).cuda()[None].repeat(B, 1, 1).contiguous()
+    m = sv.StereoSGBM_create(**kw)
+    for _ in range(2):
+        out = m.compute_batch(Lb, Rb).cpu().numpy()
+        for b in range(B):
+            assert _sha(out[b]) == golden_full["full"][name]["sha256"], f"{name}: frame {b} of the batch differs"
+    sv.release_workspaces()
