@@ -257,25 +257,19 @@ struct SweepLane {
     const int16_t *masktab;
     // loop-carried
     uint32_t h[NR];
-    uint32_t cbuf[PFD][NR], sbuf[PFD][NR];
+    static constexpr int PFS = PFD > 2 ? 2 : PFD;   // S (pass 2) is prefetched less deep than C: it is consumed at the
+                                                    // end of the step, and its registers are what pass 2 is short of
+    uint32_t cbuf[PFD][NR], sbuf[PFS][NR];
     uint32_t cap_best, cap_s2, cap_taps;
 
-    __device__ __forceinline__ void prefetch(int slot, int upf)
+    __device__ __forceinline__ size_t pix_off(int upf) const
     {
-        const int xp = xbase + xdir * min(max(upf, 0), W1 - 1);
-        const size_t off = (size_t)xp * Dp;
-        switch (slot) {   // slot is a compile-time constant at every call site
-#define SVB_PF_CASE(i)                                             \
-    case i:                                                        \
-        if (i < PFD) {                                             \
-            ld_regs_stream<NR>(Crow + off, cbuf[i < PFD ? i : 0]); \
-            if (PASS2) ld_regs_stream<NR>(Srow + off, sbuf[i < PFD ? i : 0]); \
-        }                                                          \
-        break;
-            SVB_PF_CASE(0) SVB_PF_CASE(1) SVB_PF_CASE(2) SVB_PF_CASE(3)
-#undef SVB_PF_CASE
-        }
+        return (size_t)(xbase + xdir * min(max(upf, 0), W1 - 1)) * Dp;
     }
+    template <int SLOT>
+    __device__ __forceinline__ void prefetch_c(int upf) { ld_regs_stream<NR>(Crow + pix_off(upf), cbuf[SLOT]); }
+    template <int SLOT>
+    __device__ __forceinline__ void prefetch_s(int upf) { if (PASS2) ld_regs_stream<NR>(Srow + pix_off(upf), sbuf[SLOT]); }
 
     template <int PH>
     __device__ __forceinline__ void step(const AggArgs &a, int t, int16_t *dpre, unsigned *keys)
@@ -285,8 +279,9 @@ struct SweepLane {
         const bool act = rowActive && (unsigned)u < (unsigned)W1;
         uint32_t c[NR], s[NR], L[NR];
 #pragma unroll
-        for (int k = 0; k < NR; k++) { c[k] = cbuf[PB][k]; s[k] = PASS2 ? sbuf[PB][k] : 0u; }
-        prefetch(PB, u + PFD);
+        for (int k = 0; k < NR; k++) { c[k] = cbuf[PB][k]; s[k] = (PASS2 && !SAFE) ? sbuf[PH % PFS][k] : 0u; }
+        prefetch_c<PB>(u + PFD);
+        if (!SAFE) prefetch_s<PH % PFS>(u + PFS);
         // ---- horizontal path (registers) ----
         {
             const uint32_t hm = u > 0 ? 0xFFFFFFFFu : 0u;
@@ -333,6 +328,11 @@ struct SweepLane {
             }
             st_regs_cs_pred<NR>(Srow + (size_t)(xbase + xdir * (act ? u : 0)) * Dp, s, act);
         } else {
+            if (SAFE) {   // pass-1 S joins last (plain packed adds commute): its load has the whole step to land
+#pragma unroll
+                for (int k = 0; k < NR; k++) s[k] += sbuf[PH % PFS][k];
+                prefetch_s<PH % PFS>(u + PFS);
+            }
 #pragma unroll
             for (int k = 0; k < NR; k++) {
                 if (PAD) s[k] |= 0x7FFF7FFFu & ~keep[k];
@@ -528,7 +528,12 @@ __global__ void __launch_bounds__(NGRP *G + (NV ? 32 : 0)) k_sweep(const __grid_
 #pragma unroll
     for (int k = 0; k < NR; k++) st.h[k] = 0;
 #pragma unroll
-    for (int i = 0; i < PFD; i++) st.prefetch(i, i - st.lag);
+    st.template prefetch_c<0>(0 - st.lag);
+    if (PFD > 1) st.template prefetch_c<(1 < PFD ? 1 : 0)>(1 - st.lag);
+    if (PFD > 2) st.template prefetch_c<(2 < PFD ? 2 : 0)>(2 - st.lag);
+    if (PFD > 3) st.template prefetch_c<(3 < PFD ? 3 : 0)>(3 - st.lag);
+    st.template prefetch_s<0>(0 - st.lag);
+    if (PFD > 1) st.template prefetch_s<(PFD > 1 ? 1 : 0)>(1 - st.lag);
 
     for (int t0 = 0; t0 < nsteps; t0 += AGG_UNROLL) {
 #define SVB_STEP(PH)                 \
