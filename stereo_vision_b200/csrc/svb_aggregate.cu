@@ -590,10 +590,9 @@ int svb_launch_aggregate(svb_context *ctx, const SgbmPlan &pl, char *ws, size_t 
     // reset schedulers / progress / scatter keys
     if (passes & 1) {
         SVB_CUDA_CHECK(cudaMemsetAsync(ctx->tickets, 0, 2 * sizeof(unsigned), st));
-        for (int b = 0; b < B; b++) {
-            SVB_CUDA_CHECK(cudaMemsetAsync(ws + (size_t)b * ws_stride + pl.off_prog, 0, 2 * sizeof(unsigned) * pl.nbands, st));
-            SVB_CUDA_CHECK(cudaMemsetAsync(ws + (size_t)b * ws_stride + pl.off_key, 0xFF, sizeof(unsigned) * (size_t)pl.H * pl.W, st));
-        }
+        // one strided memset per buffer for the whole batch (pitch = per-frame workspace stride)
+        SVB_CUDA_CHECK(cudaMemset2DAsync(ws + pl.off_prog, ws_stride, 0, 2 * sizeof(unsigned) * pl.nbands, B, st));
+        SVB_CUDA_CHECK(cudaMemset2DAsync(ws + pl.off_key, ws_stride, 0xFF, sizeof(unsigned) * (size_t)pl.H * pl.W, B, st));
     }
     AggArgs a;
     memset(&a, 0, sizeof a);

@@ -212,8 +212,7 @@ int svb_launch_speckle(int16_t *img, int H, int W, size_t pitch, size_t stride, 
                        int maxDiff, int32_t *labels, size_t lstride, cudaStream_t st)
 {
     dim3 grid((W + 255) / 256, H, B);
-    for (int b = 0; b < B; b++)
-        SVB_CUDA_CHECK(cudaMemsetAsync(labels + (size_t)b * lstride + (size_t)H * W, 0, sizeof(int) * (size_t)H * W, st));
+    SVB_CUDA_CHECK(cudaMemset2DAsync(labels + (size_t)H * W, lstride * sizeof(int), 0, sizeof(int) * (size_t)H * W, B, st));
     k_ccl_init<<<grid, 256, 0, st>>>(img, labels, H, W, pitch, stride, newVal, maxDiff, lstride);
     k_ccl_merge<<<grid, 256, 0, st>>>(img, labels, H, W, pitch, stride, newVal, maxDiff, lstride);
     dim3 g1((H * W + 255) / 256, 1, B);
