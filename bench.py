@@ -171,7 +171,7 @@ def run_ours(args):
     import torch
     import torch.distributed as dist
     import stereo_vision_b200 as sv
-    from stereo_vision_b200 import synth
+    from stereo_vision_b200 import shard, synth
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -221,10 +221,7 @@ def run_ours(args):
                 collect()
         e1.record()
         barrier()
-        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
-        if world > 1:
-            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-        return float(ms.item())
+        return shard.max_over_ranks(e0.elapsed_time(e1), dev)   # device time, max over ranks
 
     for _ in range(max(args.warmup, 3)):
         step_resident()
