@@ -107,6 +107,15 @@ int svb_init_undistort_rectify_map(svb_context *ctx, const double *K, const doub
 int svb_remap_u8(svb_context *ctx, const uint8_t *src, int sH, int sW, int C, size_t spitch, size_t sstride,
                  const float *mapx, const float *mapy, uint8_t *dst, int dH, int dW, size_t dpitch, size_t dstride,
                  int B, void *stream);
+/* The CV_16SC2 form of the two calls above: map1 s16 [H][W][2] = floor of the coordinate, map2 u16 [H][W] =
+ * (fy<<5)|fx, rounded from the f64 coordinate (cvRound(u*32)).  cv2.undistort(img, K, dist) is exactly these two
+ * calls with R = I, P = K (reference: calibrate_v4/distance.py:125-126, calibrate/test_calibration.py undistort). */
+int svb_init_undistort_rectify_map_fixed(svb_context *ctx, const double *K, const double *dist, int ndist,
+                                         const double *R, const double *P33, int W, int H, int16_t *map1,
+                                         uint16_t *map2, void *stream);
+int svb_remap_u8_fixed(svb_context *ctx, const uint8_t *src, int sH, int sW, int C, size_t spitch, size_t sstride,
+                       const int16_t *map1, const uint16_t *map2, uint8_t *dst, int dH, int dW, size_t dpitch,
+                       size_t dstride, int B, void *stream);
 
 /* ---- 3-D ---- */
 /* dtype: 0=u8 1=s16 2=s32 3=f32 (raw value used, no /16 — as cv2).  Q: HOST double[16]. xyz: f32 [B][H][W][3].
@@ -119,6 +128,22 @@ int svb_reproject_to_3d(svb_context *ctx, const void *disp, int dtype, int H, in
 int svb_box_median_depth(svb_context *ctx, const int16_t *disp16, int H, int W, size_t stride_elems,
                          const double *Q, int invalid16, const float *boxes, const int32_t *box_image, int nboxes,
                          float *out, void *stream);
+
+/* ---- sparse 3-D path + ingest ---- */
+/* cv2.undistortPoints(pts, K, dist, R, P) — ball_drop.py:239-240, 3dpose.py:538-549, checkerboard_distance.py:83-86.
+ * src/dst: device [n][2], dtype 3 = f32, 4 = f64; K[9], dist[ndist], R[9] (NULL = I), P33[9] = P[:, :3] (NULL = I):
+ * HOST doubles.  Five fixed-point iterations in f64, as cv2's default criteria. */
+int svb_undistort_points(svb_context *ctx, const void *src, void *dst, int dtype, int n, const double *K,
+                         const double *dist, int ndist, const double *R, const double *P33, void *stream);
+/* cv2.triangulatePoints(P1, P2, pts1, pts2) — ball_drop.py:254, 3dpose.py:553, checkerboard_distance.py:95.
+ * P1/P2: HOST double[12] (3x4 row-major); pts: device, layout 0 = [2][n] (cv2's 2xN), 1 = [n][2];
+ * out: device [4][n] homogeneous points (unit norm, sign arbitrary — callers divide by w). */
+int svb_triangulate_points(svb_context *ctx, const double *P1, const double *P2, const void *pts1, const void *pts2,
+                           int dtype, int n, int layout, void *out4xn, void *stream);
+/* cv2.cvtColor(img, COLOR_BGR2GRAY), u8: (B*3735 + G*19235 + R*9798 + 16384) >> 15.  src [B][H][spitch] BGR
+ * interleaved, dst [B][H][dpitch]. */
+int svb_bgr2gray_u8(svb_context *ctx, const uint8_t *src, uint8_t *dst, int H, int W, size_t spitch, size_t sstride,
+                    size_t dpitch, size_t dstride, int B, void *stream);
 
 /* ---- measurement helper (bench.py): device peak of packed s16x2 ALU instructions (VIADDMNMX / VIMNMX chains on
  * all SMs), in thread-level packed instructions per second; x2 = 16-bit lane operations per second.  This is the

@@ -182,3 +182,34 @@ def num_threads() -> int:
 
 def set_num_threads(n: int) -> None:
     lib().svo_set_num_threads(int(n))
+
+
+# ---- sparse 3-D path: undistortPoints / triangulatePoints / BGR2GRAY ----
+def undistort_points(src, K, dist, R=None, P=None) -> np.ndarray:
+    """f64 restatement of cv2.undistortPoints; returns float64 (N,2)."""
+    p = np.ascontiguousarray(np.asarray(src, dtype=np.float64).reshape(-1, 2))
+    K = np.ascontiguousarray(K, dtype=np.float64)
+    d = np.ascontiguousarray(np.asarray(dist, dtype=np.float64).ravel()) if dist is not None else np.zeros(0)
+    Rm = np.ascontiguousarray(R, dtype=np.float64) if R is not None else None
+    Pm = np.ascontiguousarray(np.asarray(P, dtype=np.float64)[:3, :3]) if P is not None else None
+    out = np.empty_like(p)
+    lib().svo_undistort_points(_p(p), C.c_int(len(p)), _p(K), _p(d), C.c_int(d.size), _p(Rm) if Rm is not None else None,
+                               _p(Pm) if Pm is not None else None, _p(out))
+    return out
+
+
+def triangulate_points(P1, P2, a, b) -> np.ndarray:
+    """Homogeneous 4xN (float64) DLT triangulation; a, b are (N,2)."""
+    a = np.ascontiguousarray(np.asarray(a, dtype=np.float64).reshape(-1, 2))
+    b = np.ascontiguousarray(np.asarray(b, dtype=np.float64).reshape(-1, 2))
+    P1 = np.ascontiguousarray(P1, dtype=np.float64); P2 = np.ascontiguousarray(P2, dtype=np.float64)
+    out = np.empty((len(a), 4), dtype=np.float64)
+    lib().svo_triangulate_points(_p(P1), _p(P2), _p(a), _p(b), C.c_int(len(a)), _p(out))
+    return out.T.copy()
+
+
+def bgr2gray(img) -> np.ndarray:
+    img = np.ascontiguousarray(img, dtype=np.uint8)
+    out = np.empty(img.shape[:2], dtype=np.uint8)
+    lib().svo_bgr2gray(_p(img), C.c_int(out.size), _p(out))
+    return out

@@ -625,3 +625,94 @@ void svo_set_num_threads(int n)
     (void)n;
 #endif
 }
+
+/* ================= SURVEY.md §8(f) "next" rows: the sparse 3-D path the reference runs per detection ===========
+ * cv2.undistortPoints + cv2.triangulatePoints as called by ball_drop.py:225-259 (calculate_3d_position),
+ * checkerboard_distance.py:83-103 and 3dpose.py:530-561; cv2.cvtColor(BGR2GRAY) in front of the matcher.
+ * Semantics recovered by probing the cv2 4.13.0 binary (tests/golden/make_golden.py pins them):
+ *   undistortPoints: x=(u-cx)/fx, y=(v-cy)/fy; exactly 5 fixed-point iterations of the inverse distortion in
+ *     double (default TermCriteria(COUNT,5,0.01)); then (P[:, :3]*R)*[x y 1], divide.  Bit-exact in f64.
+ *   triangulatePoints: per point the 4x4 DLT matrix [x1*P1[2]-P1[0]; y1*P1[2]-P1[1]; x2*P2[2]-P2[0]; y2*P2[2]-P2[1]],
+ *     right singular vector of the smallest singular value (sign arbitrary, callers divide by w).
+ *   BGR2GRAY (u8): (B*3735 + G*19235 + R*9798 + 16384) >> 15   (4.13 uses 15-bit coefficients).
+ */
+void svo_undistort_points(const double *src, int n, const double *K, const double *dist, int ndist, const double *R,
+                          const double *P33, double *dst)
+{
+    double k[14] = {0};
+    for (int i = 0; i < ndist && i < 14; i++) k[i] = dist[i];
+    const double fx = K[0], fy = K[4], cx = K[2], cy = K[5];
+    double RR[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1};
+    if (R) memcpy(RR, R, sizeof RR);
+    if (P33) {
+        double t[9];
+        for (int r = 0; r < 3; r++)
+            for (int c = 0; c < 3; c++) t[3 * r + c] = P33[3 * r] * RR[c] + P33[3 * r + 1] * RR[3 + c] + P33[3 * r + 2] * RR[6 + c];
+        memcpy(RR, t, sizeof RR);
+    }
+    for (int i = 0; i < n; i++) {
+        double x = (src[2 * i] - cx) / fx, y = (src[2 * i + 1] - cy) / fy;
+        const double x0 = x, y0 = y;
+        for (int it = 0; it < 5; it++) {
+            const double r2 = x * x + y * y;
+            double icdist = (1 + ((k[7] * r2 + k[6]) * r2 + k[5]) * r2) / (1 + ((k[4] * r2 + k[1]) * r2 + k[0]) * r2);
+            if (icdist < 0) { x = x0; y = y0; break; }
+            const double dx = 2 * k[2] * x * y + k[3] * (r2 + 2 * x * x) + k[8] * r2 + k[9] * r2 * r2;
+            const double dy = k[2] * (r2 + 2 * y * y) + 2 * k[3] * x * y + k[10] * r2 + k[11] * r2 * r2;
+            x = (x0 - dx) * icdist;
+            y = (y0 - dy) * icdist;
+        }
+        const double X = RR[0] * x + RR[1] * y + RR[2], Y = RR[3] * x + RR[4] * y + RR[5], Wc = RR[6] * x + RR[7] * y + RR[8];
+        const double iw = 1. / Wc;
+        dst[2 * i] = X * iw;
+        dst[2 * i + 1] = Y * iw;
+    }
+}
+
+/* one-sided Jacobi (Hestenes) on the 4x4 DLT matrix; out = V column of the smallest singular value */
+void svo_triangulate_points(const double *P1, const double *P2, const double *a, const double *b, int n, double *out4)
+{
+    for (int i = 0; i < n; i++) {
+        double A[4][4], V[4][4];
+        for (int c = 0; c < 4; c++) {
+            A[0][c] = a[2 * i] * P1[8 + c] - P1[c];
+            A[1][c] = a[2 * i + 1] * P1[8 + c] - P1[4 + c];
+            A[2][c] = b[2 * i] * P2[8 + c] - P2[c];
+            A[3][c] = b[2 * i + 1] * P2[8 + c] - P2[4 + c];
+            for (int r = 0; r < 4; r++) V[r][c] = r == c;
+        }
+        for (int sweep = 0; sweep < 30; sweep++) {
+            int rotated = 0;
+            for (int p = 0; p < 3; p++)
+                for (int q = p + 1; q < 4; q++) {
+                    double al = 0, be = 0, ga = 0;
+                    for (int r = 0; r < 4; r++) { al += A[r][p] * A[r][p]; be += A[r][q] * A[r][q]; ga += A[r][p] * A[r][q]; }
+                    if (fabs(ga) <= 1e-15 * sqrt(al * be) || ga == 0) continue;
+                    rotated = 1;
+                    const double zeta = (be - al) / (2 * ga);
+                    const double t = (zeta >= 0 ? 1. : -1.) / (fabs(zeta) + sqrt(1 + zeta * zeta));
+                    const double cs = 1. / sqrt(1 + t * t), sn = cs * t;
+                    for (int r = 0; r < 4; r++) {
+                        const double ap = A[r][p], aq = A[r][q];
+                        A[r][p] = cs * ap - sn * aq; A[r][q] = sn * ap + cs * aq;
+                        const double vp = V[r][p], vq = V[r][q];
+                        V[r][p] = cs * vp - sn * vq; V[r][q] = sn * vp + cs * vq;
+                    }
+                }
+            if (!rotated) break;
+        }
+        int best = 0; double bn = DBL_MAX;
+        for (int c = 0; c < 4; c++) {
+            double s = 0;
+            for (int r = 0; r < 4; r++) s += A[r][c] * A[r][c];
+            if (s < bn) { bn = s; best = c; }
+        }
+        for (int r = 0; r < 4; r++) out4[4 * i + r] = V[r][best];
+    }
+}
+
+void svo_bgr2gray(const uint8_t *src, int n, uint8_t *dst)
+{
+    for (int i = 0; i < n; i++)
+        dst[i] = (uint8_t)((src[3 * i] * 3735 + src[3 * i + 1] * 19235 + src[3 * i + 2] * 9798 + 16384) >> 15);
+}

@@ -29,6 +29,8 @@ EXPORTS = [
     "svb_sgbm_workspace_bytes", "svb_sgbm_compute", "svb_sgbm_debug_stages", "svb_median3_s16",
     "svb_filter_speckles_s16", "svb_init_undistort_rectify_map", "svb_remap_u8", "svb_reproject_to_3d",
     "svb_box_median_depth", "svb_set_timing", "svb_sgbm_last_stage_ms", "svb_measure_packed_alu_peak",
+    "svb_undistort_points", "svb_triangulate_points", "svb_bgr2gray_u8", "svb_init_undistort_rectify_map_fixed",
+    "svb_remap_u8_fixed",
 ]
 
 _lib = None
@@ -57,10 +59,15 @@ def load():
     lib.svb_filter_speckles_s16.argtypes = [vp, vp, i32, i32, sz, i32, sz, i32, i32, i32, vp, sz, vp]
     lib.svb_init_undistort_rectify_map.argtypes = [vp, vp, vp, i32, vp, vp, i32, i32, vp, vp, vp]
     lib.svb_remap_u8.argtypes = [vp, vp, i32, i32, i32, sz, sz, vp, vp, vp, i32, i32, sz, sz, i32, vp]
+    lib.svb_init_undistort_rectify_map_fixed.argtypes = lib.svb_init_undistort_rectify_map.argtypes
+    lib.svb_remap_u8_fixed.argtypes = lib.svb_remap_u8.argtypes
     lib.svb_reproject_to_3d.argtypes = [vp, vp, i32, i32, i32, vp, i32, vp, i32, vp, vp]
     lib.svb_box_median_depth.argtypes = [vp, vp, i32, i32, sz, vp, i32, vp, vp, i32, vp, vp]
     lib.svb_set_timing.argtypes = [vp, i32]
     lib.svb_sgbm_last_stage_ms.argtypes = [vp, C.POINTER(C.c_float), i32]
+    lib.svb_undistort_points.argtypes = [vp, vp, vp, i32, i32, vp, vp, i32, vp, vp, vp]
+    lib.svb_triangulate_points.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, vp, vp]
+    lib.svb_bgr2gray_u8.argtypes = [vp, vp, vp, i32, i32, sz, sz, sz, sz, i32, vp]
     lib.svb_measure_packed_alu_peak.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_double), vp]
     for n in EXPORTS:
         f = getattr(lib, n)

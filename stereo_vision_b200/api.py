@@ -197,10 +197,12 @@ def StereoSGBM_create(minDisparity=0, numDisparities=16, blockSize=3, P1=0, P2=0
 
 # ---------------------------------------------------------------- rectification
 def initUndistortRectifyMap(cameraMatrix, distCoeffs, R, newCameraMatrix, size, m1type=CV_32FC1, device=None):
-    """cv2.initUndistortRectifyMap(K, dist, R, P, (W,H), CV_32FC1) -> (map1, map2) float32 HxW.
+    """cv2.initUndistortRectifyMap(K, dist, R, P, (W,H), m1type) -> (map1, map2): float32 HxW each for CV_32FC1 (the
+    form the reference uses); int16 HxWx2 + uint16 HxW for CV_16SC2 (the form cv2.undistort uses internally).
     Returns NumPy maps unless `device` is given (then torch CUDA tensors that stay resident)."""
-    if m1type != CV_32FC1:
-        raise NotImplementedError("only m1type=CV_32FC1 (the only form the reference uses) is implemented")
+    if m1type not in (CV_32FC1, CV_16SC2):
+        raise NotImplementedError("only m1type=CV_32FC1 or CV_16SC2 is implemented")
+    fixed = m1type == CV_16SC2
     W, H = int(size[0]), int(size[1])
     K = np.ascontiguousarray(np.asarray(cameraMatrix, np.float64).reshape(3, 3))
     dist = np.zeros(0) if distCoeffs is None else np.ascontiguousarray(np.asarray(distCoeffs, np.float64).ravel())
@@ -214,9 +216,14 @@ def initUndistortRectifyMap(cameraMatrix, distCoeffs, R, newCameraMatrix, size, 
     keep_dev = device is not None
     dev = _device_of() if device is None else torch.device(device).index or 0
     with torch.cuda.device(dev):
-        mx = torch.empty((H, W), dtype=torch.float32, device=f"cuda:{dev}")
-        my = torch.empty_like(mx)
-        check(_lib.load().svb_init_undistort_rectify_map(
+        if fixed:
+            mx = torch.empty((H, W, 2), dtype=torch.int16, device=f"cuda:{dev}")
+            my = torch.empty((H, W), dtype=torch.uint16, device=f"cuda:{dev}")
+        else:
+            mx = torch.empty((H, W), dtype=torch.float32, device=f"cuda:{dev}")
+            my = torch.empty_like(mx)
+        fn = _lib.load().svb_init_undistort_rectify_map_fixed if fixed else _lib.load().svb_init_undistort_rectify_map
+        check(fn(
             _lib.context(dev), K.ctypes.data_as(C.c_void_p), dist.ctypes.data_as(C.c_void_p) if dist.size else None,
             int(dist.size), Rm.ctypes.data_as(C.c_void_p) if Rm is not None else None,
             P33.ctypes.data_as(C.c_void_p) if P33 is not None else None, W, H, _ptr(mx), _ptr(my), _stream(dev)))
@@ -227,18 +234,26 @@ def initUndistortRectifyMap(cameraMatrix, distCoeffs, R, newCameraMatrix, size, 
 
 def remap(src, map1, map2, interpolation=INTER_LINEAR, dst=None, borderMode=BORDER_CONSTANT, borderValue=0):
     """cv2.remap(src, map1, map2, cv2.INTER_LINEAR) for uint8 HxW / HxWx3 (or batched [B,H,W(,3)] tensors with
-    shared maps); float32 maps; BORDER_CONSTANT 0.  Bit-exact with cv2's fixed-point tables."""
+    shared maps); float32 HxW maps or the CV_16SC2 pair (int16 HxWx2, uint16 HxW); BORDER_CONSTANT 0.  Bit-exact with
+    cv2's fixed-point tables."""
     if interpolation != INTER_LINEAR or borderMode != BORDER_CONSTANT or np.any(np.asarray(borderValue) != 0):
         raise NotImplementedError("only INTER_LINEAR with BORDER_CONSTANT(0) (the reference's call) is implemented")
     if src.dtype not in (np.uint8, torch.uint8):
         raise ValueError("remap: only uint8 images are supported")
     dev = _device_of(src, map1, map2)
     S = _as_dev(src, dev, torch.uint8)
-    mx = _as_dev(map1, dev, torch.float32)
-    my = _as_dev(map2, dev, torch.float32)
-    if mx.shape != my.shape or mx.dim() != 2:
-        raise ValueError("map1/map2 must be float32 HxW arrays of equal shape")
-    dH, dW = mx.shape
+    fixed = map1.dtype in (np.int16, torch.int16)
+    if fixed:
+        mx = _as_dev(map1, dev, torch.int16)
+        my = _as_dev(map2, dev, torch.uint16)
+        if mx.dim() != 3 or mx.shape[2] != 2 or tuple(mx.shape[:2]) != tuple(my.shape):
+            raise ValueError("fixed-point maps must be int16 HxWx2 and uint16 HxW")
+    else:
+        mx = _as_dev(map1, dev, torch.float32)
+        my = _as_dev(map2, dev, torch.float32)
+        if mx.shape != my.shape or mx.dim() != 2:
+            raise ValueError("map1/map2 must be float32 HxW arrays of equal shape")
+    dH, dW = my.shape
     batched = isinstance(src, torch.Tensor) and (S.dim() == 4 or (S.dim() == 3 and S.shape[-1] not in (1, 3)))
     Sb = S if batched else S[None]
     ch = 1 if Sb.dim() == 3 else Sb.shape[3]
@@ -248,8 +263,9 @@ def remap(src, map1, map2, interpolation=INTER_LINEAR, dst=None, borderMode=BORD
     shape = (B, dH, dW) if Sb.dim() == 3 else (B, dH, dW, ch)
     with torch.cuda.device(dev):
         out = torch.empty(shape, dtype=torch.uint8, device=S.device)
-        check(_lib.load().svb_remap_u8(_lib.context(dev), _ptr(Sb), sH, sW, ch, sW * ch, sH * sW * ch, _ptr(mx), _ptr(my),
-                                       _ptr(out), dH, dW, dW * ch, dH * dW * ch, B, _stream(dev)))
+        fn = _lib.load().svb_remap_u8_fixed if fixed else _lib.load().svb_remap_u8
+        check(fn(_lib.context(dev), _ptr(Sb), sH, sW, ch, sW * ch, sH * sW * ch, _ptr(mx), _ptr(my),
+                 _ptr(out), dH, dW, dW * ch, dH * dW * ch, B, _stream(dev)))
     out = out if batched else out[0]
     return _out(out, src)
 
@@ -368,3 +384,133 @@ def packed_alu_peak(device=None) -> dict:
     rate, mhz = C.c_double(), C.c_double()
     check(_lib.load().svb_measure_packed_alu_peak(_lib.context(dev), C.byref(rate), C.byref(mhz), _stream(dev)))
     return {"packed_instr_per_s": rate.value, "ops16_per_s": 2.0 * rate.value, "sm_clock_max_mhz": mhz.value}
+
+
+# ---------------------------------------------------------------- sparse 3-D path + ingest
+COLOR_BGR2GRAY = 6
+
+
+def _host_f64(a, shape=None):
+    if a is None:
+        return None
+    a = np.ascontiguousarray(np.asarray(a, np.float64))
+    return a.reshape(shape) if shape is not None else a
+
+
+def _hp(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None and a.size else None
+
+
+def undistortPoints(src, cameraMatrix, distCoeffs, R=None, P=None):
+    """cv2.undistortPoints(src, K, dist, R=None, P=None): float32/float64 points shaped (N,1,2), (1,N,2) or (N,2);
+    same dtype out, always shaped (N,1,2) as cv2 returns it (ball_drop.py:239-240, 3dpose.py:538-549, checkerboard_distance.py:83-86)."""
+    is_t = isinstance(src, torch.Tensor)
+    dt = src.dtype
+    if dt not in (np.float32, np.float64, torch.float32, torch.float64):
+        raise ValueError("undistortPoints: points must be float32 or float64")
+    if src.shape[-1] != 2 or src.ndim not in (2, 3):
+        raise ValueError("undistortPoints: points must be shaped (N,1,2), (1,N,2) or (N,2)")
+    dev = _device_of(src)
+    S = _as_dev(src, dev)
+    n = S.numel() // 2
+    K = _host_f64(cameraMatrix, (3, 3))
+    dist = np.zeros(0) if distCoeffs is None else _host_f64(distCoeffs).ravel()
+    Rm = _host_f64(R, (3, 3)) if R is not None else None
+    P33 = None
+    if P is not None:
+        Pm = np.asarray(P, np.float64)
+        if Pm.shape not in ((3, 3), (3, 4)):
+            raise ValueError("P must be 3x3 or 3x4")
+        P33 = np.ascontiguousarray(Pm[:3, :3])
+    with torch.cuda.device(dev):
+        out = torch.empty_like(S)
+        code = 3 if S.dtype == torch.float32 else 4
+        check(_lib.load().svb_undistort_points(_lib.context(dev), _ptr(S), _ptr(out), code, n, _hp(K), _hp(dist),
+                                               int(dist.size), _hp(Rm), _hp(P33), _stream(dev)))
+    out = out.reshape(n, 1, 2)
+    return out if is_t else out.cpu().numpy()
+
+
+def triangulatePoints(projMatr1, projMatr2, projPoints1, projPoints2):
+    """cv2.triangulatePoints(P1, P2, pts1, pts2) -> 4xN homogeneous points (float32 for float32 points, else float64).
+    Points: 2xN (cv2's documented layout), (N,1,2) / (1,N,2) (what undistortPoints returns) or a single (2,) point
+    (ball_drop.py:254).  The vector is unit-norm with arbitrary sign, as with cv2: divide by row 3."""
+    is_t = isinstance(projPoints1, torch.Tensor)
+
+    def norm(p):
+        if not isinstance(p, torch.Tensor):
+            p = np.asarray(p)
+            if p.dtype not in (np.float32, np.float64):
+                p = p.astype(np.float64)
+        if p.ndim == 1 and p.shape[0] == 2:
+            return p.reshape(1, 2), 1
+        if p.ndim == 3 and p.shape[-1] == 2:
+            return p.reshape(-1, 2), 1
+        if p.ndim == 2 and p.shape[0] == 2:
+            return p, 0
+        if p.ndim == 2 and p.shape[1] == 2:
+            return p, 1
+        raise ValueError("triangulatePoints: points must be 2xN, Nx2, (N,1,2), (1,N,2) or a single (2,) point")
+    a, la = norm(projPoints1)
+    b, lb = norm(projPoints2)
+    dev = _device_of(a, b)
+    A, Bm = _as_dev(a, dev), _as_dev(b, dev)
+    if lb != la:
+        Bm = Bm.t().contiguous()
+    if A.dtype != Bm.dtype:
+        A, Bm = A.double(), Bm.double()
+    n = A.shape[1] if la == 0 else A.shape[0]
+    if (Bm.shape[1] if la == 0 else Bm.shape[0]) != n:
+        raise ValueError("triangulatePoints: both views need the same number of points")
+    P1 = _host_f64(projMatr1, (3, 4))
+    P2 = _host_f64(projMatr2, (3, 4))
+    with torch.cuda.device(dev):
+        out = torch.empty((4, n), dtype=A.dtype, device=A.device)
+        code = 3 if A.dtype == torch.float32 else 4
+        check(_lib.load().svb_triangulate_points(_lib.context(dev), _hp(P1), _hp(P2), _ptr(A), _ptr(Bm), code, n, la,
+                                                 _ptr(out), _stream(dev)))
+    return out if is_t else out.cpu().numpy()
+
+
+def cvtColor(src, code):
+    """cv2.cvtColor(img, cv2.COLOR_BGR2GRAY) for uint8 HxWx3 (or batched [B,H,W,3] tensors): cv2's 15-bit fixed point."""
+    if code != COLOR_BGR2GRAY:
+        raise NotImplementedError("only COLOR_BGR2GRAY is implemented")
+    if src.dtype not in (np.uint8, torch.uint8) or src.shape[-1] != 3 or src.ndim not in (3, 4):
+        raise ValueError("cvtColor: uint8 HxWx3 image expected")
+    dev = _device_of(src)
+    S = _as_dev(src, dev, torch.uint8)
+    Sb = S if S.dim() == 4 else S[None]
+    B, H, W = Sb.shape[0], Sb.shape[1], Sb.shape[2]
+    with torch.cuda.device(dev):
+        out = torch.empty((B, H, W), dtype=torch.uint8, device=S.device)
+        check(_lib.load().svb_bgr2gray_u8(_lib.context(dev), _ptr(Sb), _ptr(out), H, W, 3 * W, 3 * H * W, W, H * W, B,
+                                          _stream(dev)))
+    out = out if S.dim() == 4 else out[0]
+    return _out(out, src)
+
+
+def undistort(src, cameraMatrix, distCoeffs, dst=None, newCameraMatrix=None):
+    """cv2.undistort(img, K, dist[, None, newK]) = initUndistortRectifyMap(K, dist, I, newK or K, CV_16SC2) +
+    remap(INTER_LINEAR), bit-exact (calibrate_v4/distance.py:125-126).  uint8 HxW or HxWx3."""
+    if src.ndim not in (2, 3):
+        raise ValueError("undistort: HxW or HxWx3 image expected")
+    H, W = src.shape[:2]
+    dev = _device_of(src)
+    mx, my = initUndistortRectifyMap(cameraMatrix, distCoeffs, None, cameraMatrix if newCameraMatrix is None else newCameraMatrix,
+                                     (int(W), int(H)), CV_16SC2, device=f"cuda:{dev}")
+    return remap(src, mx, my, INTER_LINEAR)
+
+
+def triangulate_stereo(left_pts, right_pts, K1, d1, K2, d2, R, T):
+    """Batched form of the reference's calculate_3d_position (ball_drop.py:225-259): undistortPoints(P=K) on both views,
+    P1 = K1[I|0], P2 = K2[R|T], triangulatePoints, divide by w.  left/right points: (N,2) pixels.  Returns (N,3)."""
+    lp = np.asarray(left_pts, np.float32).reshape(-1, 1, 2) if not isinstance(left_pts, torch.Tensor) else left_pts
+    rp = np.asarray(right_pts, np.float32).reshape(-1, 1, 2) if not isinstance(right_pts, torch.Tensor) else right_pts
+    lu = undistortPoints(lp, K1, d1, P=K1)
+    ru = undistortPoints(rp, K2, d2, P=K2)
+    K1 = np.asarray(K1, np.float64); K2 = np.asarray(K2, np.float64)
+    P1 = K1 @ np.hstack((np.eye(3), np.zeros((3, 1))))
+    P2 = K2 @ np.hstack((np.asarray(R, np.float64).reshape(3, 3), np.asarray(T, np.float64).reshape(3, 1)))
+    X = triangulatePoints(P1, P2, lu, ru)
+    return (X[:3] / X[3]).T

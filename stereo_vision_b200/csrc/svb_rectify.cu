@@ -12,12 +12,8 @@ struct MapParams {
     int has_tilt;
 };
 
-__global__ void __launch_bounds__(256) k_init_undistort_rectify_map(MapParams mp, int W, int H, float *__restrict__ mapx,
-                                                                   float *__restrict__ mapy)
+__device__ __forceinline__ void map_uv(const MapParams &mp, int j, int i, double &u, double &v)
 {
-    const int j = blockIdx.x * blockDim.x + threadIdx.x;
-    const int i = blockIdx.y;
-    if (j >= W) return;
     const double *iR = mp.iR;
     const double *k = mp.k;
     // no FMA contraction: cv2 evaluates these as separate multiplies/adds
@@ -43,7 +39,6 @@ __global__ void __launch_bounds__(256) k_init_undistort_rectify_map(MapParams mp
                                               __dmul_rn(p2, _2xy)),
                                     __dmul_rn(s3, r2)),
                           __dmul_rn(s4, r4));
-    double u, v;
     if (mp.has_tilt) {
         const double *mt = mp.mt;
         double vx = __dadd_rn(__dadd_rn(__dmul_rn(mt[0], xd), __dmul_rn(mt[1], yd)), mt[2]);
@@ -56,8 +51,31 @@ __global__ void __launch_bounds__(256) k_init_undistort_rectify_map(MapParams mp
         u = __dadd_rn(__dmul_rn(mp.fx, xd), mp.cx);
         v = __dadd_rn(__dmul_rn(mp.fy, yd), mp.cy);
     }
-    mapx[(size_t)i * W + j] = (float)u;
-    mapy[(size_t)i * W + j] = (float)v;
+}
+
+// cvRound(double) on x86 (cvtsd2si): round-half-even; NaN / out of range -> 0x80000000
+__device__ __forceinline__ int cv_round_f64(double v) { return (fabs(v) < 2147483648.0) ? __double2int_rn(v) : (int)0x80000000; }
+
+// FIXED = false: CV_32FC1 maps.  FIXED = true: CV_16SC2 + CV_16UC1 (integer part as short2, 5+5-bit fractions),
+// rounded from the f64 coordinate as cv2 does — the form cv2.undistort() uses internally.
+template <bool FIXED>
+__global__ void __launch_bounds__(256) k_init_undistort_rectify_map(MapParams mp, int W, int H, void *__restrict__ m1,
+                                                                   void *__restrict__ m2)
+{
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    const int i = blockIdx.y;
+    if (j >= W) return;
+    double u, v;
+    map_uv(mp, j, i, u, v);
+    const size_t o = (size_t)i * W + j;
+    if (FIXED) {
+        const int iu = cv_round_f64(__dmul_rn(u, 32.0)), iv = cv_round_f64(__dmul_rn(v, 32.0));
+        reinterpret_cast<short2 *>(m1)[o] = make_short2((short)(iu >> 5), (short)(iv >> 5));
+        reinterpret_cast<uint16_t *>(m2)[o] = (uint16_t)((iv & 31) * 32 + (iu & 31));
+    } else {
+        reinterpret_cast<float *>(m1)[o] = (float)u;
+        reinterpret_cast<float *>(m2)[o] = (float)v;
+    }
 }
 
 static int inv3x3(const double *A, double *Ai)
@@ -92,9 +110,8 @@ static int inv3x3(const double *A, double *Ai)
     return 0;
 }
 
-extern "C" int svb_init_undistort_rectify_map(svb_context *ctx, const double *K, const double *dist, int ndist,
-                                              const double *R, const double *P33, int W, int H, float *mapx,
-                                              float *mapy, void *stream)
+static int launch_maps(svb_context *ctx, const double *K, const double *dist, int ndist, const double *R,
+                       const double *P33, int W, int H, void *mapx, void *mapy, bool fixed, void *stream)
 {
     SVB_REQUIRE(ctx && K && mapx && mapy, SVB_ERR_INVALID, "init_undistort_rectify_map: null argument");
     SVB_REQUIRE(W > 0 && H > 0, SVB_ERR_INVALID, "init_undistort_rectify_map: bad size %dx%d", W, H);
@@ -131,9 +148,26 @@ extern "C" int svb_init_undistort_rectify_map(svb_context *ctx, const double *K,
     memcpy(mp.mt, mt, sizeof mt);
     SVB_CUDA_CHECK(cudaSetDevice(ctx->device));
     dim3 grid((W + 255) / 256, H);
-    k_init_undistort_rectify_map<<<grid, 256, 0, (cudaStream_t)stream>>>(mp, W, H, mapx, mapy);
+    if (fixed)
+        k_init_undistort_rectify_map<true><<<grid, 256, 0, (cudaStream_t)stream>>>(mp, W, H, mapx, mapy);
+    else
+        k_init_undistort_rectify_map<false><<<grid, 256, 0, (cudaStream_t)stream>>>(mp, W, H, mapx, mapy);
     SVB_CUDA_CHECK(cudaGetLastError());
     return SVB_OK;
+}
+
+extern "C" int svb_init_undistort_rectify_map(svb_context *ctx, const double *K, const double *dist, int ndist,
+                                              const double *R, const double *P33, int W, int H, float *mapx,
+                                              float *mapy, void *stream)
+{
+    return launch_maps(ctx, K, dist, ndist, R, P33, W, H, mapx, mapy, false, stream);
+}
+
+extern "C" int svb_init_undistort_rectify_map_fixed(svb_context *ctx, const double *K, const double *dist, int ndist,
+                                                    const double *R, const double *P33, int W, int H, int16_t *map1,
+                                                    uint16_t *map2, void *stream)
+{
+    return launch_maps(ctx, K, dist, ndist, R, P33, W, H, map1, map2, true, stream);
 }
 
 // ---------------- remap ----------------
@@ -145,11 +179,9 @@ __device__ __forceinline__ int cv_round_x86(float v)
 __device__ __forceinline__ int sat16(int v) { return max(-32768, min(32767, v)); }
 
 template <int C>
-__device__ __forceinline__ void remap_px(const uint8_t *__restrict__ src, int sH, int sW, size_t spitch, float mx,
-                                         float my, uint8_t *o)
+__device__ __forceinline__ void remap_fixed(const uint8_t *__restrict__ src, int sH, int sW, size_t spitch, int ix, int iy,
+                                            int fx, int fy, uint8_t *o)
 {
-    const int sx = cv_round_x86(mx * 32.0f), sy = cv_round_x86(my * 32.0f);
-    const int ix = sat16(sx >> 5), iy = sat16(sy >> 5), fx = sx & 31, fy = sy & 31;
     const int w00 = (32 - fy) * (32 - fx) * 32, w01 = (32 - fy) * fx * 32, w10 = fy * (32 - fx) * 32, w11 = fy * fx * 32;
     const bool y0 = (unsigned)iy < (unsigned)sH, y1 = (unsigned)(iy + 1) < (unsigned)sH;
     const bool x0 = (unsigned)ix < (unsigned)sW, x1 = (unsigned)(ix + 1) < (unsigned)sW;
@@ -164,6 +196,14 @@ __device__ __forceinline__ void remap_px(const uint8_t *__restrict__ src, int sH
         int t11 = (y1 && x1) ? (int)__ldg(r1 + xb + c) : 0;
         o[c] = (uint8_t)((w00 * t00 + w01 * t01 + w10 * t10 + w11 * t11 + 16384) >> 15);
     }
+}
+
+template <int C>
+__device__ __forceinline__ void remap_px(const uint8_t *__restrict__ src, int sH, int sW, size_t spitch, float mx,
+                                         float my, uint8_t *o)
+{
+    const int sx = cv_round_x86(mx * 32.0f), sy = cv_round_x86(my * 32.0f);
+    remap_fixed<C>(src, sH, sW, spitch, sat16(sx >> 5), sat16(sy >> 5), sx & 31, sy & 31, o);
 }
 
 // one thread = 4 consecutive destination pixels (vector map loads, word stores when aligned)
@@ -219,6 +259,44 @@ extern "C" int svb_remap_u8(svb_context *ctx, const uint8_t *src, int sH, int sW
     else
         k_remap_u8<3><<<grid, 128, 0, (cudaStream_t)stream>>>(src, sH, sW, spitch, sstride, mapx, mapy, dst, dH, dW,
                                                              dpitch, dstride, vec_ok);
+    SVB_CUDA_CHECK(cudaGetLastError());
+    return SVB_OK;
+}
+
+// remap with CV_16SC2 + CV_16UC1 fixed-point maps (one thread per destination pixel; the second half of cv2.undistort)
+template <int C>
+__global__ void __launch_bounds__(256) k_remap_u8_fixed(const uint8_t *__restrict__ src, int sH, int sW, size_t spitch,
+                                                        size_t sstride, const short2 *__restrict__ map1,
+                                                        const uint16_t *__restrict__ map2, uint8_t *__restrict__ dst,
+                                                        int dW, size_t dpitch, size_t dstride)
+{
+    const int x = blockIdx.x * blockDim.x + threadIdx.x;
+    const int y = blockIdx.y;
+    if (x >= dW) return;
+    const short2 xy = __ldg(map1 + (size_t)y * dW + x);
+    const int f = __ldg(map2 + (size_t)y * dW + x) & 1023;
+    uint8_t o[C];
+    remap_fixed<C>(src + (size_t)blockIdx.z * sstride, sH, sW, spitch, xy.x, xy.y, f & 31, f >> 5, o);
+    uint8_t *d = dst + (size_t)blockIdx.z * dstride + (size_t)y * dpitch + (size_t)x * C;
+#pragma unroll
+    for (int c = 0; c < C; c++) d[c] = o[c];
+}
+
+extern "C" int svb_remap_u8_fixed(svb_context *ctx, const uint8_t *src, int sH, int sW, int C, size_t spitch,
+                                  size_t sstride, const int16_t *map1, const uint16_t *map2, uint8_t *dst, int dH, int dW,
+                                  size_t dpitch, size_t dstride, int B, void *stream)
+{
+    SVB_REQUIRE(ctx && src && map1 && map2 && dst, SVB_ERR_INVALID, "remap: null argument");
+    SVB_REQUIRE(C == 1 || C == 3, SVB_ERR_INVALID, "remap: only 1- or 3-channel u8 images (got C=%d)", C);
+    SVB_REQUIRE(sH > 0 && sW > 0 && dH > 0 && dW > 0 && B > 0, SVB_ERR_INVALID, "remap: bad size");
+    SVB_REQUIRE(sH < 32768 && sW < 32768, SVB_ERR_INVALID, "remap: source larger than SHRT_MAX (cv2 asserts too)");
+    SVB_CUDA_CHECK(cudaSetDevice(ctx->device));
+    dim3 grid((dW + 255) / 256, dH, B);
+    const short2 *m1 = reinterpret_cast<const short2 *>(map1);
+    if (C == 1)
+        k_remap_u8_fixed<1><<<grid, 256, 0, (cudaStream_t)stream>>>(src, sH, sW, spitch, sstride, m1, map2, dst, dW, dpitch, dstride);
+    else
+        k_remap_u8_fixed<3><<<grid, 256, 0, (cudaStream_t)stream>>>(src, sH, sW, spitch, sstride, m1, map2, dst, dW, dpitch, dstride);
     SVB_CUDA_CHECK(cudaGetLastError());
     return SVB_OK;
 }
