@@ -8,5 +8,6 @@ from .api import (  # noqa: F401
     COLOR_BGR2GRAY, cvtColor, triangulatePoints, triangulate_stereo, undistort, undistortPoints,
 )
 from ._lib import SvbError  # noqa: F401
+from .calib import StereoRig, load_calibration  # noqa: F401
 
 __version__ = "0.1.0"

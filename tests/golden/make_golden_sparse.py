@@ -48,6 +48,13 @@ def cases():
     out["bgr_small"] = synth.stereo_pair(120, 200, 32, seed=7, channels=3)[0]
     out["lp"] = (rng.random((40, 2)) * [1400, 800] + [260, 140]).astype(np.float32)
     out["rp"] = out["lp"] - np.array([60.0, 0.5], np.float32)
+    # small rig for the loader / rectify glue (checkerboard_distance.py:49-103)
+    k1, e1, k2, e2, r, t = synth.synthetic_rig(320, 180)
+    out["rig"] = {"left_matrix": k1, "left_dist": np.asarray(e1, np.float64), "right_matrix": k2,
+                  "right_dist": np.asarray(e2, np.float64), "R": r, "T": np.asarray(t, np.float64).reshape(3, 1)}
+    out["rig_left"], out["rig_right"] = synth.stereo_pair(180, 320, 32, seed=11, channels=3)
+    out["rig_lp"] = (rng.random((54, 2)) * [200, 120] + [60, 30]).astype(np.float32)
+    out["rig_rp"] = out["rig_lp"] - np.array([9.0, 0.2], np.float32)
     return out
 
 
@@ -76,6 +83,22 @@ def main():
         h = cv2.triangulatePoints(P1, P2, lu, ru)
         pos.append((h[:3] / h[3]).reshape(3))
     g["calc3d"] = np.array(pos)
+    # loader / rectify glue: stereoRectify(alpha=0) -> maps -> remap; corners -> undistortPoints(R1,P1) -> triangulate
+    rg = c["rig"]
+    R1, R2, Pr1, Pr2, Q, _, _ = cv2.stereoRectify(rg["left_matrix"], rg["left_dist"], rg["right_matrix"], rg["right_dist"],
+                                                 (320, 180), rg["R"], rg["T"], alpha=0.0)
+    g.update(rig_R1=R1, rig_R2=R2, rig_P1=Pr1, rig_P2=Pr2, rig_Q=Q)
+    ml = cv2.initUndistortRectifyMap(rg["left_matrix"], rg["left_dist"], R1, Pr1, (320, 180), cv2.CV_32FC1)
+    mr = cv2.initUndistortRectifyMap(rg["right_matrix"], rg["right_dist"], R2, Pr2, (320, 180), cv2.CV_32FC1)
+    g["rig_rect_left"] = cv2.remap(c["rig_left"], ml[0], ml[1], cv2.INTER_LINEAR)
+    g["rig_rect_right"] = cv2.remap(c["rig_right"], mr[0], mr[1], cv2.INTER_LINEAR)
+    lu = cv2.undistortPoints(c["rig_lp"].reshape(-1, 1, 2), rg["left_matrix"], rg["left_dist"], R=R1, P=Pr1)
+    ru = cv2.undistortPoints(c["rig_rp"].reshape(-1, 1, 2), rg["right_matrix"], rg["right_dist"], R=R2, P=Pr2)
+    pos = []
+    for j in range(lu.shape[0]):
+        h = cv2.triangulatePoints(Pr1, Pr2, lu[j, 0].reshape(2, 1), ru[j, 0].reshape(2, 1))
+        pos.append((h[:3] / h[3]).reshape(3))
+    g["rig_pts3d"] = np.array(pos)
     np.savez_compressed(os.path.join(HERE, "golden_sparse.npz"), **g)
     print("wrote", len(g), "arrays, cv2", cv2.__version__)
 
