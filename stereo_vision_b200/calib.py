@@ -8,7 +8,7 @@ Reference interfaces mirrored here:
   StereoRig.rectify / depth / boxes    checkerboard_distance.py:71-72 (remap), ball_drop.py:225-259 (3-D per detection)
 
 `cv2.stereoRectify` is calibration-time host work (north_star: the calibration scripts stay on the host unchanged):
-pass its outputs in, or let `from_calibration` call the host's cv2 when it is importable.  Nothing here runs per frame
+pass its outputs in, or hand `from_calibration` the host function (`stereo_rectify=cv2.stereoRectify`).  Nothing here runs per frame
 on the CPU.
 """
 from __future__ import annotations
@@ -66,18 +66,15 @@ def load_calibration(test_dir):
             "right_dist": right_dist, "R": R, "T": T}
 
 
-def _host_stereo_rectify(calib, image_size, alpha, flags):
-    try:
-        import cv2  # host-side calibration library of the reference; never used per frame
-    except ImportError as e:
-        raise RuntimeError("stereoRectify is calibration-time host work: pass rectification=(R1, R2, P1, P2, Q) "
-                           "or make cv2 importable on the host") from e
-    R1, R2, P1, P2, Q, _, _ = cv2.stereoRectify(
+def _host_stereo_rectify(stereo_rectify, calib, image_size, alpha, flags):
+    """One call of the host's stereoRectify (e.g. `cv2.stereoRectify`, handed in by the caller: this package never
+    imports the CPU library) with the reference's argument order (checkerboard_distance.py:49-51)."""
+    out = stereo_rectify(
         np.asarray(calib["left_matrix"], np.float64), np.asarray(calib["left_dist"], np.float64),
         np.asarray(calib["right_matrix"], np.float64), np.asarray(calib["right_dist"], np.float64),
         tuple(int(v) for v in image_size), np.asarray(calib["R"], np.float64),
         np.asarray(calib["T"], np.float64).reshape(3, 1), flags=flags, alpha=alpha)
-    return R1, R2, P1, P2, Q
+    return tuple(out[:5])
 
 
 class StereoRig:
@@ -102,14 +99,18 @@ class StereoRig:
         self.matcher = matcher
 
     @classmethod
-    def from_calibration(cls, calib, image_size, alpha=0.0, flags=CALIB_ZERO_DISPARITY, rectification=None, device=None,
-                         matcher=None):
-        """image_size = (width, height) as for cv2.  `rectification` = (R1, R2, P1, P2, Q) from cv2.stereoRectify; when
-        omitted the host's cv2 is asked for it once (checkerboard_distance.py:49-51: alpha=0.0)."""
+    def from_calibration(cls, calib, image_size, alpha=0.0, flags=CALIB_ZERO_DISPARITY, rectification=None,
+                         stereo_rectify=None, device=None, matcher=None):
+        """image_size = (width, height) as for cv2.  Give either `rectification` = (R1, R2, P1, P2, Q) as returned by
+        cv2.stereoRectify, or `stereo_rectify=cv2.stereoRectify` to have it called once here with `alpha`/`flags`
+        (checkerboard_distance.py:49-51: alpha=0.0)."""
         if calib is None:
             raise ValueError("no calibration (load_calibration returned None)")
         if rectification is None:
-            rectification = _host_stereo_rectify(calib, image_size, alpha, flags)
+            if stereo_rectify is None:
+                raise ValueError("stereoRectify is calibration-time host work: pass rectification=(R1, R2, P1, P2, Q) "
+                                 "or stereo_rectify=cv2.stereoRectify")
+            rectification = _host_stereo_rectify(stereo_rectify, calib, image_size, alpha, flags)
         return cls(calib, image_size, rectification, device=device, matcher=matcher)
 
     @classmethod

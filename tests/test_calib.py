@@ -91,8 +91,11 @@ def test_gpu_rig_rectify_and_triangulate(sv, tmp_path):
 
 @pytest.mark.gpu
 def test_gpu_rig_host_stereo_rectify(sv):
-    """from_calibration without `rectification` asks the host's cv2 once (calibration-time)."""
-    pytest.importorskip("cv2")
-    rig = calib.StereoRig.from_calibration(RIG, (320, 180), alpha=0.0)
+    """from_calibration(stereo_rectify=cv2.stereoRectify) calls the host function once (calibration-time)."""
+    cv2 = pytest.importorskip("cv2")
+    with pytest.raises(ValueError):
+        calib.StereoRig.from_calibration(RIG, (320, 180))
+    rig = calib.StereoRig.from_calibration(RIG, (320, 180), alpha=0.0, flags=cv2.CALIB_ZERO_DISPARITY,
+                                           stereo_rectify=cv2.stereoRectify)
     for k in ("R1", "R2", "P1", "P2", "Q"):
         assert np.allclose(getattr(rig, k), G[f"rig_{k}"], rtol=1e-12, atol=1e-12), k
