@@ -172,6 +172,10 @@ int svo_sgbm_cost_volume(const uint8_t *left, const uint8_t *right, int H, int W
             crow[i] = (int16_t)s; /* wraps like cv2's int16 cost type if bs>=15 */
         }
     }
+    /* MODE_HH4 (cv2 4.13.0, probed: tests/golden/make_golden.py mode-3 cases): rows whose block window leaves the
+     * image at the bottom (y + r > H-1) never get a cost — the volume stays 0 there. */
+    if (p.mode == 3 && r > 0)
+        for (int y = imax(H - r, 0); y < H; y++) memset(Cvol + (size_t)y * rowsz, 0, rowsz * sizeof(int16_t));
     free(Lp); free(Rp); free(pix); free(hs);
     return 0;
 }
@@ -264,8 +268,20 @@ int svo_sgbm_aggregate_dirs(const int16_t *Cvol, int H, int W1, int D, int P1, i
     for (int i = 0; i < ndirs && i < 8; i++) aggregate_dir(Cvol, S, H, W1, D, dirs[i][0], dirs[i][1], P1, P2);
     return 0;
 }
+/* any subset of the 8 directions: bit i of mask = dirs[i] (0 left, 1 up-left, 2 up, 3 up-right, 4 right, 5 down-right,
+ * 6 down, 7 down-left predecessor). */
+int svo_sgbm_aggregate_mask(const int16_t *Cvol, int H, int W1, int D, int P1, int P2, int mask, int16_t *S)
+{
+    memset(S, 0, sizeof(int16_t) * (size_t)H * W1 * D);
+    static const int dirs[8][2] = {{-1, 0}, {-1, -1}, {0, -1}, {1, -1}, {1, 0}, {1, 1}, {0, 1}, {-1, 1}};
+    for (int i = 0; i < 8; i++)
+        if (mask >> i & 1) aggregate_dir(Cvol, S, H, W1, D, dirs[i][0], dirs[i][1], P1, P2);
+    return 0;
+}
 int svo_sgbm_aggregate(const int16_t *Cvol, int H, int W1, int D, int P1, int P2, int mode, int16_t *S)
 {
+    /* MODE_HH4: left, up, right, down (4 paths); MODE_HH: all 8; MODE_SGBM: left, up-left, up, up-right, right */
+    if (mode == 3) return svo_sgbm_aggregate_mask(Cvol, H, W1, D, P1, P2, 0x55, S);
     return svo_sgbm_aggregate_dirs(Cvol, H, W1, D, P1, P2, mode == 1 ? 8 : 5, S);
 }
 
@@ -393,7 +409,7 @@ int svo_sgbm_compute(const uint8_t *left, const uint8_t *right, int H, int W, in
 {
     svo_params p;
     svo_resolve_params(praw, &p);
-    if (p.mode != 0 && p.mode != 1) return -3;
+    if (p.mode != 0 && p.mode != 1 && p.mode != 3) return -3;
     const int minD = p.minDisparity, D = p.numDisparities, maxD = minD + D;
     const int minX1 = imax(maxD, 0), maxX1 = W + imin(minD, 0), W1 = maxX1 - minX1;
     if (D <= 0) return -1;

@@ -307,6 +307,7 @@ struct SweepLane {
             int16_t *eptr = edge_out + (size_t)(act ? u : 0) * 3 * Dp;
 #pragma unroll
             for (int j = 0; j < 3; j++) {
+                if (NV == 1 && j != 1) continue;   // MODE_HH4: the vertical predecessor only
                 const int offv = (((PH + 1 + j) & (AGG_SLOTS - 1)) * 3 + j) * VS;          // written 3-j steps ago
                 const int offe = (((PH + AGG_ENS - 1 + j) & (AGG_ENS - 1)) * 3 + j) * VS;  // pixel u-1+j, u == t
                 const int16_t *src = prevL + (isRow0 ? offe : offv);
@@ -380,6 +381,7 @@ __device__ __forceinline__ void cta_barrier() { asm volatile("bar.sync 0;" ::: "
 #endif
 
 // NV = 3: wavefront sweep with the three vertical/diagonal predecessors (+ one DMA warp per CTA);
+// NV = 1: same machinery, vertical predecessor only (MODE_HH4: 2 + 2 paths);
 // NV = 0: horizontal path only (rows independent; the 5th path of MODE_SGBM), no barriers, no DMA warp.
 template <int NR, int G, int NGRP, int NV, bool PASS2, bool SAFE, bool PAD, int PFD>
 __global__ void __launch_bounds__(NGRP *G + (NV ? 32 : 0)) k_sweep(const __grid_constant__ AggArgs a)
@@ -616,13 +618,17 @@ int svb_launch_aggregate(svb_context *ctx, const SgbmPlan &pl, char *ws, size_t 
     a.prog = (unsigned *)(ws + pl.off_prog);
     a.ticket = ctx->tickets;
     int rc = SVB_OK;
-    if (passes & 1) rc = launch_sweep<3, false>(pl.safe, pad, NR, pl.G, a, pl.nbands * B, st);
+    const bool hh4 = pl.p.mode == 3;   // left + up, then right + down
+    if (passes & 1)
+        rc = hh4 ? launch_sweep<1, false>(pl.safe, pad, NR, pl.G, a, pl.nbands * B, st)
+                 : launch_sweep<3, false>(pl.safe, pad, NR, pl.G, a, pl.nbands * B, st);
     if (rc || !(passes & 2)) return rc;
     a.flip = 1;
-    if (pl.p.mode == 1) {   // MODE_HH: right, down-right, down, down-left + selection
+    if (pl.p.mode == 1 || hh4) {   // MODE_HH: right, down-right, down, down-left + selection; MODE_HH4: right, down
         a.prog = (unsigned *)(ws + pl.off_prog) + pl.nbands;
         a.ticket = ctx->tickets + 1;
-        rc = launch_sweep<3, true>(pl.safe, pad, NR, pl.G, a, pl.nbands * B, st);
+        rc = hh4 ? launch_sweep<1, true>(pl.safe, pad, NR, pl.G, a, pl.nbands * B, st)
+                 : launch_sweep<3, true>(pl.safe, pad, NR, pl.G, a, pl.nbands * B, st);
     } else {                // MODE_SGBM: 5th path (from the right) + selection, rows independent
         rc = launch_sweep<0, true>(pl.safe, pad, NR, pl.G, a, pl.nbands * B, st);
     }

@@ -92,8 +92,8 @@ int svb_make_plan(const svb_sgbm_params *raw, int H, int W, int ch, SgbmPlan *pl
     SVB_REQUIRE(ch == 1 || ch == 3, SVB_ERR_INVALID, "sgbm: images must be CV_8UC1 or CV_8UC3 (channels=%d)", ch);
     SVB_REQUIRE(H > 0 && W > 0, SVB_ERR_INVALID, "sgbm: bad image size %dx%d", W, H);
     SVB_REQUIRE(p.numDisparities > 0, SVB_ERR_INVALID, "sgbm: numDisparities must be positive (got %d)", p.numDisparities);
-    SVB_REQUIRE(p.mode == 0 || p.mode == 1, SVB_ERR_UNSUPPORTED,
-                "sgbm: mode %d not implemented (MODE_SGBM=0 and MODE_HH=1 only)", p.mode);
+    SVB_REQUIRE(p.mode == 0 || p.mode == 1 || p.mode == 3, SVB_ERR_UNSUPPORTED,
+                "sgbm: mode %d not implemented (MODE_SGBM=0, MODE_HH=1 and MODE_HH4=3 only)", p.mode);
     pl->H = H; pl->W = W; pl->ch = ch;
     const int minD = p.minDisparity, D = p.numDisparities, maxD = minD + D;
     pl->D = D;

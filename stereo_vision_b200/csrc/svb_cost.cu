@@ -190,7 +190,7 @@ template <int NPL, int R>
 __global__ void __launch_bounds__(COST_THREADS) k_cost_fused(const uint4 *__restrict__ LP, const int16_t *__restrict__ RP,
                                                              int16_t *__restrict__ Cv, int H, int W1, int Wr, int Dp,
                                                              int D, int G, int jb0, int TXP, int rows_per_seg,
-                                                             uint32_t cpad, size_t ws_stride)
+                                                             uint32_t cpad, int zrow, size_t ws_stride)
 {
     constexpr int BS = 2 * R + 1;
     extern __shared__ __align__(16) unsigned char csm[];
@@ -252,6 +252,7 @@ __global__ void __launch_bounds__(COST_THREADS) k_cost_fused(const uint4 *__rest
         // ---- phase 2 ----
         const bool emit = r >= ya + R;
         const int y = r - R;
+        const uint32_t live = y < zrow ? 0xFFFFFFFFu : 0u;   // MODE_HH4: rows whose window leaves the image stay 0
         if (c0 < TX && x0 + c0 < W1) {
             // pix column of output column c, offset dx: tile-local index c+dx, clamped to the valid columns
             auto pixcol = [&](int ci) -> const int16_t * {
@@ -280,10 +281,10 @@ __global__ void __launch_bounds__(COST_THREADS) k_cost_fused(const uint4 *__rest
                     acc[k][2] += hs[2] - old.z; acc[k][3] += hs[3] - old.w;     // acc >= old per half: no borrow
                     if (emit) {
                         uint4 o;
-                        o.x = (acc[k][0] & keep[0]) | (cpad & ~keep[0]);
-                        o.y = (acc[k][1] & keep[1]) | (cpad & ~keep[1]);
-                        o.z = (acc[k][2] & keep[2]) | (cpad & ~keep[2]);
-                        o.w = (acc[k][3] & keep[3]) | (cpad & ~keep[3]);
+                        o.x = (acc[k][0] & keep[0] & live) | (cpad & ~keep[0]);
+                        o.y = (acc[k][1] & keep[1] & live) | (cpad & ~keep[1]);
+                        o.z = (acc[k][2] & keep[2] & live) | (cpad & ~keep[2]);
+                        o.w = (acc[k][3] & keep[3] & live) | (cpad & ~keep[3]);
                         *reinterpret_cast<uint4 *>(Cv + ((size_t)y * W1 + x0 + c) * Dp + lane * 8) = o;
                     }
                 }
@@ -329,7 +330,7 @@ static int launch_cost_fused(const SgbmPlan &pl, const CostGeom &g, char *ws, si
     dim3 grid(g.ntiles, g.nseg, B);
     kern<<<grid, COST_THREADS, g.smem, st>>>((const uint4 *)(ws + pl.off_lplanes), (const int16_t *)(ws + pl.off_rplanes),
                                              (int16_t *)(ws + pl.off_C), pl.H, pl.W1, pl.Wr, pl.Dp, pl.D, pl.Dp / 8, jb0,
-                                             g.TXP, g.rows_per_seg, cpad, ws_stride);
+                                             g.TXP, g.rows_per_seg, cpad, pl.p.mode == 3 ? pl.H - pl.R : pl.H, ws_stride);
     SVB_CUDA_CHECK(cudaGetLastError());
     return SVB_OK;
 }

@@ -7,14 +7,14 @@ import numpy as np
 from stereo_vision_b200 import synth
 
 
-def sgbm_small_cases(n: int = 96):
+def sgbm_small_cases(n: int = 96, seed: int = 20261104, modes=(0, 1)):
     """Random sweep over the SURVEY.md §8c matrix; all in-contract (maxC + P2 <= 32767)."""
-    rng = np.random.default_rng(20261104)
+    rng = np.random.default_rng(seed)
     out = []
     it = 0
     while len(out) < n:
         it += 1
-        mode = int(rng.integers(0, 2)); minD = int(rng.choice([-4, 0, 4])); D = int(rng.choice([16, 24, 32, 48, 64]))
+        mode = int(modes[int(rng.integers(0, len(modes)))]); minD = int(rng.choice([-4, 0, 4])); D = int(rng.choice([16, 24, 32, 48, 64]))
         bs = int(rng.choice([1, 3, 5, 7, 9, 11])); cap = int(rng.choice([0, 31, 63])); uq = int(rng.choice([0, 5, 10, 15]))
         d12 = int(rng.choice([0, 1, 2, 3])); ch = int(rng.choice([1, 3]))
         kind = str(rng.choice(["smooth", "noise", "binary"]))
@@ -31,6 +31,11 @@ def sgbm_small_cases(n: int = 96):
             continue
         out.append(dict(kw=kw, H=H, W=W, ch=ch, kind=kind, seed=it))
     return out
+
+
+def sgbm_hh4_cases(n: int = 40):
+    """Same matrix for MODE_HH4 (mode 3)."""
+    return sgbm_small_cases(n, seed=20261105, modes=(3,))
 
 
 def sgbm_inputs(case):

@@ -124,3 +124,27 @@ def test_full_size_batch_is_race_free(sv, golden_full, name, B):
         for b in range(B):
             assert _sha(out[b]) == golden_full["full"][name]["sha256"], f"{name}: frame {b} of the batch differs"
     sv.release_workspaces()
+
+
+def test_mode_hh4_matches_cv2_golden(sv):
+    """MODE_HH4 (mode 3): small sweep bit-exact vs cv2 golden vectors, c3 at full size vs the cv2 hash, batched."""
+    import json
+    import os
+    import torch
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "golden_hh4.npz"))
+    bad = []
+    for i, c in enumerate(cases.sgbm_hh4_cases()):
+        L, R = cases.sgbm_inputs(c)
+        got = sv.StereoSGBM_create(**c["kw"]).compute(L, R)
+        if not np.array_equal(got, g[f"hh4_{i}"]):
+            bad.append((i, c, int((got != g[f"hh4_{i}"]).sum())))
+    assert not bad, f"{len(bad)} of 40 MODE_HH4 cases differ from cv2 golden: {bad[:3]}"
+    with open(os.path.join(os.path.dirname(__file__), "golden", "golden_hh4_full.json")) as f:
+        full = json.load(f)
+    L, R, kw = cases.full_inputs("c3")
+    m = sv.StereoSGBM_create(**dict(kw, mode=sv.STEREO_SGBM_MODE_HH4))
+    assert _sha(m.compute(L, R)) == full["c3_hh4"]
+    Lb = torch.from_numpy(np.stack([L] * 3)).cuda()
+    Rb = torch.from_numpy(np.stack([R] * 3)).cuda()
+    out = m.compute_batch(Lb, Rb).cpu().numpy()
+    assert all(_sha(out[b]) == full["c3_hh4"] for b in range(3))

@@ -76,3 +76,17 @@ def test_box_median_semantics():
     assert np.isnan(out[1])
     sub = (disp[4:7, 4:7][disp[4:7, 4:7] != -16] / 16.0)
     assert out[2] == np.float32(np.median((500.0 / (sub / 100.0)).astype(np.float32)))
+
+
+def test_sgbm_hh4_small_sweep_and_full_hash():
+    """MODE_HH4 (mode 3; SURVEY.md §8f row 4): 4 paths, bottom blockSize//2 rows of the cost volume stay 0."""
+    import json
+    import os
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "golden_hh4.npz"))
+    for i, c in enumerate(cases.sgbm_hh4_cases()):
+        L, R = cases.sgbm_inputs(c)
+        assert np.array_equal(oracle.sgbm_compute(L, R, **c["kw"]), g[f"hh4_{i}"]), (i, c)
+    with open(os.path.join(os.path.dirname(__file__), "golden", "golden_hh4_full.json")) as f:
+        full = json.load(f)
+    L, R, kw = cases.full_inputs("c3")
+    assert _sha(oracle.sgbm_compute(L, R, **dict(kw, mode=3))) == full["c3_hh4"]
