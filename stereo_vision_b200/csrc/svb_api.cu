@@ -132,7 +132,7 @@ int svb_make_plan(const svb_sgbm_params *raw, int H, int W, int ch, SgbmPlan *pl
     auto take = [&](size_t bytes) { size_t o = off; off = svb_align_up(off + std::max<size_t>(bytes, 16), 256); return o; };
     const size_t vol = (size_t)H * pl->W1 * pl->Dp * 2;
     pl->off_lplanes = take((size_t)H * pl->nplanes * pl->W1 * 16);
-    pl->off_rplanes = take((size_t)H * pl->nplanes * 32 * (pl->Wr + 8) * 2 + 64);   // [H][plane][8 copies][4 arrays][Wr+8]
+    pl->off_rplanes = take((size_t)H * pl->nplanes * 32 * (pl->Wr + 8) * 2 + 64);   // [H][plane][4 arrays][Wr windows] uint4 (fits: 64*Wr <= 64*(Wr+8))
     pl->off_C = take(vol);
     pl->off_S = take(vol);
     pl->off_edge = take((size_t)std::max(pl->nbands - 1, 1) * pl->W1 * 3 * pl->Dp * 2);

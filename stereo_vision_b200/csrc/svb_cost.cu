@@ -4,9 +4,10 @@
 //   k_planes : u8 images -> per-pixel BT operands, already widened to packed s16x2 so the cost kernel's inner
 //              loop is pure DPX/VIADD work:
 //                left  LP[y][pl][xi]          = uint4 { (u,u), (255-u,255-u), (u0,u0), (255-u1,255-u1) }
-//                right RP[y][pl][copy 8][arr 4][Wr+8] = int16 arrays V, 255-V, V0, 255-V1 stored REVERSED in x
-//                                               (index j = W-1-x); copy c holds element j at position j-c+8, so a
-//                                               run of 8 disparities starting at any j is one aligned LDG.128.
+//                right RP[y][pl][arr 4][w < Wr] = uint4: elements j = w..w+7 of the int16 arrays V, 255-V, V0, 255-V1
+//                                               stored REVERSED in x (index j = W-1-x): the 8 disparities of any
+//                                               window w are one aligned LDG.128, and consecutive windows (consecutive
+//                                               lanes of the cost kernel) are consecutive 16-byte words.
 //   k_cost_fused : BT pixel cost for 8 disparities per cell (4 packed registers), 2R+1 box sum in x through a
 //              shared-memory pix row, running box sum in y through a shared-memory ring -> C (written once),
 //              padded disparities overwritten with CPAD
@@ -16,6 +17,7 @@
 //   X = max(u+v1', v0+u'), Y = max(v+u1', u0+v')            -> 2 VIADD + 2 VIADDMNMX + 1 VIMNMX + 1 VIADDMNMX.RELU
 #include "svb_common.cuh"
 #include <algorithm>
+#include <cstdlib>
 
 
 __device__ __forceinline__ int grad_at(const uint8_t *rc, const uint8_t *rn, const uint8_t *rs, int x, int W, int C,
@@ -42,9 +44,8 @@ __device__ __forceinline__ uint32_t dup16(int v) { return (uint32_t)v * 0x10001u
 
 // One CTA per image row.  Per plane: plane values of both images are staged in shared memory once, the left BT
 // operands go out as one uint4 per column, the right operands are built reversed in x in shared memory and then
-// written as 8 copies, copy c shifted so that a disparity run starting at reversed index j0 with j0 % 8 == c is
-// 16-byte aligned: the cost kernel reads every right operand with one coalesced LDG.128 per lane.
-//   RP[y][plane][copy c][array a][Wr8],  element j of array a sits at position j - c + 8 of copy c.
+// written once per window: RP[y][plane][array a][w] = elements w..w+7, so the cost kernel reads every right operand
+// with one LDG.128 per lane, 128 contiguous bytes per quarter warp.
 #define PLANES_THREADS 256
 __global__ void __launch_bounds__(PLANES_THREADS) k_planes(const uint8_t *__restrict__ left, const uint8_t *__restrict__ right,
                                                            int H, int W, int C, size_t pitch, size_t istride, int ftzero,
@@ -58,7 +59,6 @@ __global__ void __launch_bounds__(PLANES_THREADS) k_planes(const uint8_t *__rest
     uint8_t *pvR = pvL + ((W + 15) & ~15);                    // [W]
     const int y = blockIdx.x, b = blockIdx.y, tid = threadIdx.x;
     const int NPL = 2 * C;
-    const int Wr8 = Wr + 8;
     left += (size_t)b * istride;
     right += (size_t)b * istride;
     LP = reinterpret_cast<uint4 *>(reinterpret_cast<char *>(LP) + (size_t)b * ws_stride);
@@ -95,22 +95,16 @@ __global__ void __launch_bounds__(PLANES_THREADS) k_planes(const uint8_t *__rest
             A[i] = (int16_t)v; A[Wa + i] = (int16_t)vn; A[2 * Wa + i] = (int16_t)v0; A[3 * Wa + i] = (int16_t)v1n;
         }
         __syncthreads();
-        // 8 shifted copies, 16 bytes per store
-        const int nq = Wr8 / 8;
-        int16_t *outp = RP + ((size_t)y * NPL + pl) * 32 * Wr8;
-        for (int i = tid; i < 4 * nq; i += PLANES_THREADS) {
-            const int a = i / nq, q = i - a * nq;
-            const uint4 va = *reinterpret_cast<const uint4 *>(A + (size_t)a * Wa + 8 * q);
-            const uint4 vb = *reinterpret_cast<const uint4 *>(A + (size_t)a * Wa + 8 * q + 8);
-            const uint32_t w[8] = {va.x, va.y, va.z, va.w, vb.x, vb.y, vb.z, vb.w};
-#pragma unroll
-            for (int c = 0; c < 8; c++) {
-                uint32_t o[4];
-#pragma unroll
-                for (int k = 0; k < 4; k++)
-                    o[k] = (c & 1) ? __byte_perm(w[c / 2 + k], w[c / 2 + k + 1], 0x5432) : w[c / 2 + k];
-                *reinterpret_cast<uint4 *>(outp + ((size_t)c * 4 + a) * Wr8 + 8 * q) = make_uint4(o[0], o[1], o[2], o[3]);
-            }
+        // one uint4 per window (8 consecutive reversed elements), consecutive windows by consecutive threads:
+        // 5 aligned words from the staged array, shifted by half a word for odd windows
+        uint4 *outp = reinterpret_cast<uint4 *>(RP) + ((size_t)y * NPL + pl) * 4 * Wr;
+        for (int i = tid; i < 4 * Wr; i += PLANES_THREADS) {
+            const int a = i / Wr, w = i - a * Wr;
+            const uint32_t *src = reinterpret_cast<const uint32_t *>(A + (size_t)a * Wa) + ((w + 8) >> 1);
+            const uint32_t sel = (w & 1) ? 0x5432u : 0x3210u;
+            const uint32_t w0 = src[0], w1 = src[1], w2 = src[2], w3 = src[3], w4 = src[4];
+            outp[i] = make_uint4(__byte_perm(w0, w1, sel), __byte_perm(w1, w2, sel), __byte_perm(w2, w3, sel),
+                                 __byte_perm(w3, w4, sel));
         }
     }
 }
@@ -133,224 +127,460 @@ int svb_launch_planes(const SgbmPlan &pl, const uint8_t *left, const uint8_t *ri
 }
 
 // ---- fused cost kernel: BT pixel cost -> horizontal box sum -> vertical running box sum -> C ----
-// One CTA owns a tile of TX = TXP-2R output columns x all disparities and marches down a segment of rows.
-// Per input row r (clamped to the image: cost-space border replication):
-//   phase 1 (window-mapped): the right-image operands of a cell (column xc, disparities 8l..8l+7) are the 8 reversed
-//            pixels starting at w = jb0 - xc + 8l, so all cells on the diagonal xc - 8l = const share them.  A thread
-//            owns one window w: it loads the 4 operand arrays x NPL planes once (aligned LDG.128 from copy w%8,
-//            prefetched one row ahead) and computes every cell of its diagonal inside the tile (<= TXP/8+1 cells),
-//            parking the pixel costs in a double-buffered shared-memory row (column stride Dp+8: conflict-free).
-//   phase 2 (column-mapped): lane l of column block cb walks CPB adjacent output columns with a running sum of the
-//            2R+1 neighbouring pix columns (Hs), swaps Hs into the cell's private slot of a (2R+1)-row ring in
-//            shared memory and updates the vertical running sum acc += Hs(r) - Hs(r-(2R+1)); from the (2R+1)-th
-//            row on it writes C[r-R][x][8l..8l+8).
+// The right-image operands of a cell (column x, disparities 8l..8l+7) are the 8 reversed pixels starting at window
+// w = jb0 - x + 8l: all cells on the diagonal x - 8l = const share them.  A CTA therefore owns a PARALLELOGRAM of the
+// (x, d) plane: NW consecutive windows x all G = Dp/8 disparity groups, i.e. for group l the NW columns
+// x = T0 - R + 8l + ci, ci in [0, NW).  Every window has exactly G cells, so phase 1 is perfectly balanced, and for a
+// fixed l the tile is a contiguous run of columns, which is all the box sums need.  Per input row r (clamped to the
+// image: cost-space border replication):
+//   phase 1: thread (ci, part) holds window ci's operands in registers (4 arrays x NPL planes, aligned LDG.128 from
+//            copy w%8, prefetched one row ahead) and computes its CPT = G/NPART cells l = part*CPT.., parking the pixel
+//            costs in a double-buffered shared-memory row pix[ci][l] (column stride Dp+8: conflict-free).
+//   phase 2: lane l of column block cb owns CPB adjacent output columns of group l: running sum of the 2R+1
+//            neighbouring pix columns (clamped per lane to the image: border replication), swapped into the cell's slot
+//            of a (2R+1)-row ring in shared memory, vertical running sum acc += Hs(r) - Hs(r-(2R+1)); from the
+//            (2R+1)-th row on it writes C[r-R][x][8l..8l+8), x = T0 + 8l + c.
 // The horizontal sums never touch HBM; C is written exactly once (2 B per pixel-disparity).
-#define COST_THREADS 352
-#define COST_CPB_MAX 6   // output columns per thread (phase 2)
+#define COST_ROLE 256    // threads per role (phase 1 / phase 2)
+#ifndef COST_WS
+#define COST_WS 0        // 1: warp-specialised variant (512 threads); measured slower, kept for experiments
+#endif
+#define COST_CPB_MAX 8   // output columns per thread (phase 2)
+#define COST_CPT_MAX 8   // cells per thread (phase 1)
+#ifndef COST_P2_COLS
+#define COST_P2_COLS 4   // columns per phase-2 pass (register footprint of the consumer role)
+#endif
 
 template <int NPL>
 struct CostWindow { uint4 v[NPL][4]; };   // [plane][V, 255-V, V0, 255-V1]
 
+// rb: this thread's window in copy w%8 of plane 0 / array 0 of the row; (plane, array) strides are CTA-uniform
 template <int NPL>
-__device__ __forceinline__ void load_window(CostWindow<NPL> &cw, const int16_t *__restrict__ RProw, int Wr8, int w)
+__device__ __forceinline__ void load_window(CostWindow<NPL> &cw, const char *__restrict__ rb, uint32_t arr_bytes)
 {
-    const int cpy = w & 7;
-    const int16_t *rb = RProw + (size_t)cpy * 4 * Wr8 + (w - cpy + 8);
 #pragma unroll
     for (int pl = 0; pl < NPL; pl++)
 #pragma unroll
         for (int a = 0; a < 4; a++)
-            cw.v[pl][a] = __ldg(reinterpret_cast<const uint4 *>(rb + ((size_t)pl * 32 + a) * Wr8));
+            cw.v[pl][a] = __ldg(reinterpret_cast<const uint4 *>(rb + (size_t)((pl * 4 + a) * arr_bytes)));
 }
 
 __device__ __forceinline__ uint32_t u4get(const uint4 &q, int i) { return i == 0 ? q.x : i == 1 ? q.y : i == 2 ? q.z : q.w; }
 
+__device__ __forceinline__ uint4 ldg_nc_pred(const void *p, bool pred)
+{
+    uint4 v;   // volatile: the asm loads/stores keep program order, which is how the kernel software-pipelines them
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.s32 p, %5, 0;\n\t@p ld.global.nc.v4.u32 {%0, %1, %2, %3}, [%4];\n\t}"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p), "r"((int)pred));
+    return v;
+}
+__device__ __forceinline__ void sts128_pred(uint32_t saddr, const uint32_t (&v)[4], bool pred)
+{
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.s32 p, %5, 0;\n\t@p st.shared.v4.u32 [%0], {%1, %2, %3, %4};\n\t}"
+                 ::"r"(saddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"((int)pred) : "memory");
+}
+__device__ __forceinline__ uint4 lds128(uint32_t saddr)
+{
+    uint4 v;
+    asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(saddr));
+    return v;
+}
+__device__ __forceinline__ void sts128(uint32_t saddr, uint32_t a, uint32_t b, uint32_t c, uint32_t d)
+{
+    asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(saddr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+
+// BT cost of one cell (8 disparities = 4 packed registers) summed over the planes; plain `+` where no half can carry
 template <int NPL>
-__device__ __forceinline__ void pix_cell(const CostWindow<NPL> &cw, const uint4 *__restrict__ LPx, int W1, uint32_t (&acc)[4])
+__device__ __forceinline__ void pix_cell(const CostWindow<NPL> &cw, const uint4 (&Lw)[NPL], uint32_t (&acc)[4])
 {
 #pragma unroll
     for (int i = 0; i < 4; i++) acc[i] = 0;
 #pragma unroll
     for (int pl = 0; pl < NPL; pl++) {
-        const uint4 Lw = __ldg(LPx + (size_t)pl * W1);
 #pragma unroll
         for (int i = 0; i < 4; i++) {
-            const uint32_t Bv = __vadd2(u4get(cw.v[pl][2], i), Lw.y);                 // v0 + (255-u)
-            const uint32_t X = __viaddmax_s16x2(Lw.x, u4get(cw.v[pl][3], i), Bv);     // max(u + 255-v1, .)
-            const uint32_t Ev = __vadd2(Lw.z, u4get(cw.v[pl][1], i));                 // u0 + (255-v)
-            const uint32_t Y = __viaddmax_s16x2(u4get(cw.v[pl][0], i), Lw.w, Ev);     // max(v + 255-u1, .)
-            uint32_t c = __viaddmax_s16x2_relu(__vmins2(X, Y), 0xFF01FF01u, 0u);      // max(min-255, 0)
+            const uint32_t Bv = u4get(cw.v[pl][2], i) + Lw[pl].y;                         // v0 + (255-u)
+            const uint32_t X = __viaddmax_s16x2(Lw[pl].x, u4get(cw.v[pl][3], i), Bv);     // max(u + 255-v1, .)
+            const uint32_t Ev = Lw[pl].z + u4get(cw.v[pl][1], i);                         // u0 + (255-v)
+            const uint32_t Y = __viaddmax_s16x2(u4get(cw.v[pl][0], i), Lw[pl].w, Ev);     // max(v + 255-u1, .)
+            uint32_t c = __viaddmax_s16x2_relu(__vmins2(X, Y), 0xFF01FF01u, 0u);          // max(min-255, 0)
             if (pl & 1) c = (c >> 2) & 0x3FFF3FFFu;
-            acc[i] = __vadd2(acc[i], c);
+            acc[i] += c;
         }
     }
 }
 
+struct CostArgs {
+    const uint4 *LP; const int16_t *RP; int16_t *Cv;
+    int H, W1, Wr, Dp, D, G, jb0, NW, NPART, CPT, NCB, rows_per_seg, zrow;
+    uint32_t cpad;
+    size_t ws_stride;
+};
+
+// phase 2 for one thread, one input row, NC adjacent output columns starting at tile column c0 + kofs.  One code path
+// for every lane (border lanes clamp their pix columns and mask their stores): all consumer warps take the same time,
+// which is what the producer/consumer pipeline wants.  All shared-memory reads are issued up front (the asm loads keep
+// program order): the ring cells that leave the window, then the NC + BS - 1 pix columns.
+struct CostP2 {
+    uint32_t pbs;        // pix row buffer (shared address) + lane*16
+    uint32_t PS2;        // pix column stride in bytes
+    uint32_t ringcell;   // ring slot cell of column c0 (shared address, + lane*16)
+    uint32_t Dp2;
+    int c0, cilo, cihi, lane, D;
+    uint32_t cmask, cpad;
+    bool live, padded;
+};
+__device__ __forceinline__ uint4 lds128_pred(uint32_t saddr, bool pred)
+{
+    uint4 v;
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.s32 p, %5, 0;\n\t@p ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];\n\t}"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(saddr), "r"((int)pred));
+    return v;
+}
+__device__ __forceinline__ void sts128_pred4(uint32_t saddr, uint32_t a, uint32_t b, uint32_t c, uint32_t d, bool pred)
+{
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.s32 p, %5, 0;\n\t@p st.shared.v4.u32 [%0], {%1, %2, %3, %4};\n\t}"
+                 ::"r"(saddr), "r"(a), "r"(b), "r"(c), "r"(d), "r"((int)pred) : "memory");
+}
+__device__ __forceinline__ void stg128_pred(void *p, uint32_t a, uint32_t b, uint32_t c, uint32_t d, bool pred)
+{
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.s32 p, %5, 0;\n\t@p st.global.v4.u32 [%0], {%1, %2, %3, %4};\n\t}"
+                 ::"l"(p), "r"(a), "r"(b), "r"(c), "r"(d), "r"((int)pred) : "memory");
+}
+template <int BS, int NC, bool EMIT>
+__device__ __forceinline__ void cost_phase2(const CostP2 &q, int kofs, int16_t *cout, uint32_t (*acc)[4])
+{
+    const uint32_t cmask = q.cmask >> kofs;
+    const uint32_t ringcell = q.ringcell + (uint32_t)kofs * q.Dp2;
+    uint4 old[NC];
+#pragma unroll
+    for (int k = 0; k < NC; k++) old[k] = lds128_pred(ringcell + (uint32_t)k * q.Dp2, cmask >> k & 1);
+    uint4 pv[NC + BS - 1];
+#pragma unroll
+    for (int i = 0; i < NC + BS - 1; i++)
+        pv[i] = lds128(q.pbs + (uint32_t)min(max(q.c0 + kofs + i, q.cilo), q.cihi) * q.PS2);
+    uint32_t hs[4] = {0, 0, 0, 0};
+#pragma unroll
+    for (int dx = 0; dx < BS; dx++) { hs[0] += pv[dx].x; hs[1] += pv[dx].y; hs[2] += pv[dx].z; hs[3] += pv[dx].w; }
+#pragma unroll
+    for (int k = 0; k < NC; k++) {
+        if (k > 0) {   // slide the window one column to the right (per-half sums < 2^15: no carry / borrow)
+            hs[0] += pv[k + BS - 1].x - pv[k - 1].x; hs[1] += pv[k + BS - 1].y - pv[k - 1].y;
+            hs[2] += pv[k + BS - 1].z - pv[k - 1].z; hs[3] += pv[k + BS - 1].w - pv[k - 1].w;
+        }
+        const bool v = cmask >> k & 1;      // columns that are not real keep meaningless sums and store nothing
+        sts128_pred4(ringcell + (uint32_t)k * q.Dp2, hs[0], hs[1], hs[2], hs[3], v);
+        acc[k][0] += hs[0] - old[k].x; acc[k][1] += hs[1] - old[k].y;
+        acc[k][2] += hs[2] - old[k].z; acc[k][3] += hs[3] - old[k].w;     // acc >= old per half: no borrow
+        if (EMIT) {
+            uint32_t o[4] = {acc[k][0], acc[k][1], acc[k][2], acc[k][3]};
+            if (!q.live) o[0] = o[1] = o[2] = o[3] = 0;      // MODE_HH4: rows whose window leaves the image stay 0
+            if (q.padded) {                                     // padded disparities carry CPAD (CTA-uniform branch)
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    const uint32_t keep = ((q.lane * 8 + 2 * j < q.D) ? 0x0000FFFFu : 0u) |
+                                          ((q.lane * 8 + 2 * j + 1 < q.D) ? 0xFFFF0000u : 0u);
+                    o[j] = (o[j] & keep) | (q.cpad & ~keep);
+                }
+            }
+            stg128_pred(reinterpret_cast<char *>(cout) + (size_t)k * q.Dp2, o[0], o[1], o[2], o[3], v);
+        }
+    }
+}
+template <int BS, bool EMIT>
+__device__ __forceinline__ void cost_phase2_row(const CostP2 &q, int16_t *cout, uint32_t (&acc)[COST_CPB_MAX][4])
+{
+    constexpr int NC = COST_P2_COLS;
+    if (EMIT) asm volatile("" : "+l"(cout));   // one pointer for the row: keep it out of the per-column blocks
+#pragma unroll
+    for (int h = 0; h < COST_CPB_MAX / NC; h++)
+        cost_phase2<BS, NC, EMIT>(q, h * NC, reinterpret_cast<int16_t *>(reinterpret_cast<char *>(cout) + (size_t)(h * NC) * q.Dp2),
+                                  acc + h * NC);
+}
+
+// left-image operands of two cells (k0, k0+1) x two planes
+struct CostLeft { uint4 v[2][2]; };
+__device__ __forceinline__ void load_left(CostLeft &L, const uint4 *LPx, int W1, int k0, uint32_t vmask)
+{
+#pragma unroll
+    for (int c = 0; c < 2; c++)
+#pragma unroll
+        for (int pl = 0; pl < 2; pl++) L.v[c][pl] = ldg_nc_pred(LPx + (size_t)pl * W1 + 8 * (k0 + c), vmask >> (k0 + c) & 1);
+}
+__device__ __forceinline__ void cells2(const CostWindow<2> &cur, const CostLeft &L, uint32_t sts, int k0, uint32_t vmask,
+                                       bool accumulate)
+{
+#pragma unroll
+    for (int c = 0; c < 2; c++) {
+        uint32_t p[4];
+        pix_cell<2>(cur, L.v[c], p);
+        if (accumulate) {
+            const uint4 prev = lds128(sts + 16u * (k0 + c));     // in-bounds even when the cell is not valid
+            p[0] += prev.x; p[1] += prev.y; p[2] += prev.z; p[3] += prev.w;
+        }
+        sts128_pred(sts + 16u * (k0 + c), p, vmask >> (k0 + c) & 1);
+    }
+}
+
+// named barriers (id 0 is __syncthreads): FULL[b] producers arrive / consumers wait, EMPTY[b] the reverse
+__device__ __forceinline__ void bar_sync(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
+__device__ __forceinline__ void bar_arrive(int id, int n) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(n) : "memory"); }
+#define COST_BAR_FULL 1    // +buffer
+#define COST_BAR_EMPTY 3   // +buffer
+#define COST_BAR_CONS 5
+
+struct CostTile {   // per-CTA geometry shared by both roles
+    int G, Dp, NW, TX, W1, H, PS, T0, ya, yb, r0, r1;
+    uint32_t smem0, pix_bytes;
+};
+
+// ---- producer role (phase 1): window ci of the tile, cells l = l0 .. l0+CPT-1 ----
 template <int NPL, int R>
-__global__ void __launch_bounds__(COST_THREADS) k_cost_fused(const uint4 *__restrict__ LP, const int16_t *__restrict__ RP,
-                                                             int16_t *__restrict__ Cv, int H, int W1, int Wr, int Dp,
-                                                             int D, int G, int jb0, int TXP, int rows_per_seg,
-                                                             uint32_t cpad, int zrow, size_t ws_stride)
+struct CostProducer {
+    static constexpr int NCH = NPL / 2;
+    // the window registers hold ONE channel (gradient + intensity plane) at a time; for 3-channel input the pixel
+    // cost accumulates in the thread's own shared-memory cells, and the next chunk's operands load while one computes
+    CostWindow<2> cur;
+    CostLeft LA;
+    const uint4 *LPt;
+    const char *rb0;
+    size_t rrow_bytes;
+    uint32_t arr_bytes, sts0, vmask;
+    bool work;
+
+    __device__ __forceinline__ void init(const CostArgs &a, const CostTile &t, int tid, int b)
+    {
+        static_assert(COST_CPT_MAX == 8, "phase 1 is written for 8 cells per thread");
+        const uint4 *LP = reinterpret_cast<const uint4 *>(reinterpret_cast<const char *>(a.LP) + (size_t)b * a.ws_stride);
+        const char *RP = reinterpret_cast<const char *>(a.RP) + (size_t)b * a.ws_stride;
+        const int ci = tid % t.NW, part = tid / t.NW;
+        const bool p1 = part < a.NPART;
+        const int l0 = part * a.CPT;
+        const int wld = min(max(a.jb0 - (t.T0 - R + ci), 0), a.Wr - 8);   // clamped: out-of-range windows own no valid cell
+        const int xf = t.T0 - R + ci + 8 * l0;                            // column of the thread's first cell
+        vmask = 0;
+#pragma unroll
+        for (int k = 0; k < COST_CPT_MAX; k++)
+            if (p1 && k < a.CPT && (unsigned)(xf + 8 * k) < (unsigned)t.W1) vmask |= 1u << k;
+        work = vmask != 0;
+        sts0 = t.smem0 + (uint32_t)(ci * t.PS + l0 * 8) * 2u;
+        arr_bytes = (uint32_t)a.Wr * 16u;                                 // one array of one plane: Wr windows
+        rrow_bytes = (size_t)NPL * 4 * arr_bytes;
+        rb0 = RP + (size_t)wld * 16;
+        LPt = LP + xf;
+        if (work) {
+            const int rc0 = max(0, min(t.H - 1, t.r0));
+            load_window<2>(cur, rb0 + (size_t)rc0 * rrow_bytes, arr_bytes);
+            load_left(LA, LPt + (size_t)rc0 * NPL * t.W1, t.W1, 0, vmask);
+        }
+    }
+    // writes pix row r into buffer buf; `signal()` runs when the row is complete (before the next operands are fetched)
+    template <typename F>
+    __device__ __forceinline__ void row(const CostTile &t, int r, int buf, F signal)
+    {
+        const int rc = max(0, min(t.H - 1, r));
+        const uint32_t sts = sts0 + (uint32_t)buf * t.pix_bytes;
+#pragma unroll 1
+        for (int ch = 0; ch < NCH; ch++) {
+            const bool last = ch + 1 == NCH;
+            if (work) {   // 8 cells in pairs, the left operands two pairs ahead
+                CostLeft LB;
+                const uint4 *LPx = LPt + ((size_t)rc * NPL + 2 * ch) * t.W1;
+                load_left(LB, LPx, t.W1, 2, vmask);
+                cells2(cur, LA, sts, 0, vmask, ch > 0);
+                load_left(LA, LPx, t.W1, 4, vmask);
+                cells2(cur, LB, sts, 2, vmask, ch > 0);
+                load_left(LB, LPx, t.W1, 6, vmask);
+                cells2(cur, LA, sts, 4, vmask, ch > 0);
+                cells2(cur, LB, sts, 6, vmask, ch > 0);
+            }
+            if (last) signal();
+            if (work && (!last || r < t.r1)) {                            // next chunk's operands
+                const int rn = max(0, min(t.H - 1, last ? r + 1 : r)), chn = last ? 0 : ch + 1;
+                load_window<2>(cur, rb0 + (size_t)rn * rrow_bytes + (size_t)(chn * 8) * arr_bytes, arr_bytes);
+                load_left(LA, LPt + ((size_t)rn * NPL + 2 * chn) * t.W1, t.W1, 0, vmask);
+            }
+        }
+    }
+};
+
+// ---- consumer role (phase 2): lane l of column block cb, COST_CPB_MAX columns ----
+template <int R>
+struct CostConsumer {
+    static constexpr int BS = 2 * R + 1;
+    CostP2 q;
+    uint32_t acc[COST_CPB_MAX][4];
+    uint32_t pix0, ringcell0, slot_bytes;
+    int16_t *cout0;
+    size_t crow;
+    int slot, zrow;
+
+    __device__ __forceinline__ uint32_t ring0(const CostTile &t) const { return t.smem0 + 2u * t.pix_bytes; }
+    __device__ __forceinline__ void init(const CostArgs &a, const CostTile &t, int tid, int b)
+    {
+        int16_t *Cv = reinterpret_cast<int16_t *>(reinterpret_cast<char *>(a.Cv) + (size_t)b * a.ws_stride);
+        const int lane = tid % t.G, cb = tid / t.G;
+        const int c0 = cb * COST_CPB_MAX;
+        const int xl = t.T0 + 8 * lane;                                    // x of output column 0 of this lane
+        uint32_t cmask = 0;
+#pragma unroll
+        for (int k = 0; k < COST_CPB_MAX; k++)
+            if (cb < a.NCB && c0 + k < t.TX && (unsigned)(xl + c0 + k) < (unsigned)t.W1) cmask |= 1u << k;
+        const uint32_t Dp2 = (uint32_t)t.Dp * 2u;
+        q.PS2 = (uint32_t)t.PS * 2u; q.Dp2 = Dp2;
+        q.c0 = c0; q.lane = lane; q.D = a.D;
+        q.cilo = min(max(R - xl, 0), t.NW - 1); q.cihi = min(max(t.W1 - 1 - xl + R, 0), t.NW - 1);
+        q.cmask = cmask; q.cpad = a.cpad; q.padded = a.D != t.Dp;
+        pix0 = t.smem0 + (uint32_t)lane * 16u;
+        ringcell0 = ring0(t) + (uint32_t)(c0 * t.Dp + lane * 8) * 2u;
+        slot_bytes = (uint32_t)t.TX * Dp2;
+        cout0 = Cv + ((ptrdiff_t)(xl + c0)) * t.Dp + lane * 8;
+        crow = (size_t)t.W1 * Dp2;
+        slot = 0; zrow = a.zrow;
+#pragma unroll
+        for (int k = 0; k < COST_CPB_MAX; k++)
+#pragma unroll
+            for (int j = 0; j < 4; j++) acc[k][j] = 0;
+    }
+    __device__ __forceinline__ void row(const CostTile &t, int r, int buf)
+    {
+        // keep the per-thread constants opaque inside the loop: hoisting every clamped column index and mask bit out of
+        // it costs ~40 registers (spills); recomputing them per row costs a few ALU instructions
+        asm volatile("" : "+r"(q.cilo), "+r"(q.cihi), "+r"(q.cmask), "+r"(q.c0));
+        if (q.cmask) {
+            const int y = r - R;
+            q.pbs = pix0 + (uint32_t)buf * t.pix_bytes;
+            q.ringcell = ringcell0 + (uint32_t)slot * slot_bytes;
+            q.live = y < zrow;
+            int16_t *cout = reinterpret_cast<int16_t *>(reinterpret_cast<char *>(cout0) + (ptrdiff_t)y * (ptrdiff_t)crow);
+            if (r >= t.ya + R) cost_phase2_row<BS, true>(q, cout, acc);
+            else cost_phase2_row<BS, false>(q, cout, acc);
+        }
+        slot = slot + 1 == BS ? 0 : slot + 1;
+    }
+};
+
+// WS = false: every thread plays both roles, one __syncthreads per row (the pix row is double-buffered).
+// WS = true : warp-specialised, threads [0, COST_ROLE) produce, [COST_ROLE, 2*COST_ROLE) consume, named barriers.
+template <int NPL, int R, int GT, bool WS>   // GT: compile-time G (0 = runtime)
+__global__ void __launch_bounds__(WS ? 2 * COST_ROLE : COST_ROLE, 1) k_cost_fused(const __grid_constant__ CostArgs a)
 {
     constexpr int BS = 2 * R + 1;
     extern __shared__ __align__(16) unsigned char csm[];
-    const int TX = TXP - 2 * R;
-    const int PS = Dp + 8;                                                 // pix column stride (elements)
-    int16_t *pixbuf = reinterpret_cast<int16_t *>(csm);                    // [2][TXP][PS]
-    int16_t *ring = pixbuf + (size_t)2 * TXP * PS;                         // [BS][TX][Dp]
-    const int b = blockIdx.z, tid = threadIdx.x;
-    const int x0 = blockIdx.x * TX;
-    const int ya = blockIdx.y * rows_per_seg, yb = min(ya + rows_per_seg, H);
-    const int Wr8 = Wr + 8;
-    LP = reinterpret_cast<const uint4 *>(reinterpret_cast<const char *>(LP) + (size_t)b * ws_stride);
-    RP = reinterpret_cast<const int16_t *>(reinterpret_cast<const char *>(RP) + (size_t)b * ws_stride);
-    Cv = reinterpret_cast<int16_t *>(reinterpret_cast<char *>(Cv) + (size_t)b * ws_stride);
-    {   // ring starts at zero: "subtract the row that leaves the window" is then unconditional
-        uint4 *rz = reinterpret_cast<uint4 *>(ring);
-        const int n = BS * TX * Dp / 8;
-        for (int i = tid; i < n; i += COST_THREADS) rz[i] = make_uint4(0, 0, 0, 0);
-    }
-    // ---- phase-1 role: window w = wmin + tid; valid pix columns of the tile are [xlo, xhi] ----
-    const int xlo = max(x0 - R, 0), xhi = min(x0 - R + TXP - 1, W1 - 1);
-    const int w = jb0 - xhi + tid;
-    const bool hasWin = tid < (xhi - xlo) + 8 * (G - 1) + 1;
-    // cells of this window: xc = jb0 - w + 8l in [xlo, xhi], l in [0, G)
-    const int xb = jb0 - w;                                 // column of l = 0 (<= xhi)
-    const int l_lo = max(0, (xlo - xb + 7) >> 3), l_hi = hasWin ? min(G - 1, (xhi - xb) >> 3) : -1;
-    // ---- phase-2 role: lane l of column block cb ----
-    const int lane = tid % G, cb = tid / G, NCB = COST_THREADS / G;
-    const int CPB = (TX + NCB - 1) / NCB;
-    const int c0 = cb * CPB;                                // first output column (tile-local) of this thread
-    uint32_t keep[4];
-#pragma unroll
-    for (int k = 0; k < 4; k++)
-        keep[k] = ((lane * 8 + 2 * k < D) ? 0x0000FFFFu : 0u) | ((lane * 8 + 2 * k + 1 < D) ? 0xFFFF0000u : 0u);
-    uint32_t acc[COST_CPB_MAX][4];
-#pragma unroll
-    for (int k = 0; k < COST_CPB_MAX; k++)
-#pragma unroll
-        for (int q = 0; q < 4; q++) acc[k][q] = 0;
-    int slot = 0;
-    const int r0 = ya - R, r1 = yb - 1 + R;
-    CostWindow<NPL> cur, nxt;
-    if (hasWin) load_window<NPL>(cur, RP + (size_t)max(0, min(H - 1, r0)) * NPL * 32 * Wr8, Wr8, w);
-    for (int r = r0; r <= r1; r++) {
-        const int rc = max(0, min(H - 1, r));
-        int16_t *pb = pixbuf + (size_t)((r - r0) & 1) * TXP * PS;
-        // ---- phase 1 ----
-        {
-            const uint4 *LProw = LP + (size_t)rc * NPL * W1;
-            for (int l = l_lo; l <= l_hi; l++) {
-                const int xc = xb + 8 * l;
-                uint32_t p[4];
-                pix_cell<NPL>(cur, LProw + xc, W1, p);
-                *reinterpret_cast<uint4 *>(pb + (size_t)(xc - (x0 - R)) * PS + l * 8) = make_uint4(p[0], p[1], p[2], p[3]);
-            }
-            if (hasWin && r < r1) load_window<NPL>(nxt, RP + (size_t)max(0, min(H - 1, r + 1)) * NPL * 32 * Wr8, Wr8, w);
+    CostTile t;
+    t.G = GT ? GT : a.G; t.Dp = t.G * 8;
+    t.NW = a.NW; t.TX = t.NW - 2 * R; t.W1 = a.W1; t.H = a.H;
+    t.PS = t.Dp + 8;                                                       // pix column stride (elements)
+    t.smem0 = (uint32_t)__cvta_generic_to_shared(csm);                     // pix [2][NW][PS], then ring [BS][TX][Dp]
+    t.pix_bytes = (uint32_t)(t.NW * t.PS) * 2u;
+    t.T0 = blockIdx.x * t.TX - 8 * (t.G - 1);                              // x of output column 0 of group 0
+    t.ya = blockIdx.y * a.rows_per_seg; t.yb = min(t.ya + a.rows_per_seg, t.H);
+    t.r0 = t.ya - R; t.r1 = t.yb - 1 + R;
+    const int b = blockIdx.z;
+    const int nring = BS * t.TX * t.Dp / 8;   // ring starts at zero: "subtract the row that leaves the window" is unconditional
+    if (!WS) {
+        CostProducer<NPL, R> P;
+        CostConsumer<R> C;
+        for (int i = threadIdx.x; i < nring; i += COST_ROLE) sts128(C.ring0(t) + 16u * i, 0, 0, 0, 0);
+        P.init(a, t, threadIdx.x, b);
+        C.init(a, t, threadIdx.x, b);
+        for (int r = t.r0; r <= t.r1; r++) {
+            const int buf = (r - t.r0) & 1;
+            P.row(t, r, buf, [] {});
+            __syncthreads();
+            C.row(t, r, buf);
         }
-        __syncthreads();
-        // ---- phase 2 ----
-        const bool emit = r >= ya + R;
-        const int y = r - R;
-        const uint32_t live = y < zrow ? 0xFFFFFFFFu : 0u;   // MODE_HH4: rows whose window leaves the image stay 0
-        if (c0 < TX && x0 + c0 < W1) {
-            // pix column of output column c, offset dx: tile-local index c+dx, clamped to the valid columns
-            auto pixcol = [&](int ci) -> const int16_t * {
-                const int x = max(xlo, min(xhi, x0 - R + ci));
-                return pb + (size_t)(x - (x0 - R)) * PS + lane * 8;
-            };
-            uint32_t hs[4] = {0, 0, 0, 0};
-#pragma unroll
-            for (int dx = 0; dx < BS; dx++) {
-                const uint4 v = *reinterpret_cast<const uint4 *>(pixcol(c0 + dx));
-                hs[0] += v.x; hs[1] += v.y; hs[2] += v.z; hs[3] += v.w;   // per-half sums < 2^15: no carry
-            }
-#pragma unroll
-            for (int k = 0; k < COST_CPB_MAX; k++) {
-                const int c = c0 + k;
-                if (k < CPB && c < TX && x0 + c < W1) {
-                    if (k > 0) {   // slide the window one column to the right
-                        const uint4 vin = *reinterpret_cast<const uint4 *>(pixcol(c + BS - 1));
-                        const uint4 vout = *reinterpret_cast<const uint4 *>(pixcol(c - 1));
-                        hs[0] += vin.x - vout.x; hs[1] += vin.y - vout.y; hs[2] += vin.z - vout.z; hs[3] += vin.w - vout.w;
-                    }
-                    uint4 *cell = reinterpret_cast<uint4 *>(ring + ((size_t)slot * TX + c) * Dp + lane * 8);
-                    const uint4 old = *cell;
-                    *cell = make_uint4(hs[0], hs[1], hs[2], hs[3]);
-                    acc[k][0] += hs[0] - old.x; acc[k][1] += hs[1] - old.y;
-                    acc[k][2] += hs[2] - old.z; acc[k][3] += hs[3] - old.w;     // acc >= old per half: no borrow
-                    if (emit) {
-                        uint4 o;
-                        o.x = (acc[k][0] & keep[0] & live) | (cpad & ~keep[0]);
-                        o.y = (acc[k][1] & keep[1] & live) | (cpad & ~keep[1]);
-                        o.z = (acc[k][2] & keep[2] & live) | (cpad & ~keep[2]);
-                        o.w = (acc[k][3] & keep[3] & live) | (cpad & ~keep[3]);
-                        *reinterpret_cast<uint4 *>(Cv + ((size_t)y * W1 + x0 + c) * Dp + lane * 8) = o;
-                    }
-                }
-            }
+    } else if (threadIdx.x < COST_ROLE) {
+        CostProducer<NPL, R> P;
+        P.init(a, t, threadIdx.x, b);
+        for (int r = t.r0; r <= t.r1; r++) {
+            const int it = r - t.r0, buf = it & 1;
+            if (it >= 2) bar_sync(COST_BAR_EMPTY + buf, 2 * COST_ROLE);    // consumers are done with row it-2
+            P.row(t, r, buf, [&] { bar_arrive(COST_BAR_FULL + buf, 2 * COST_ROLE); });
         }
-        slot = slot + 1 == BS ? 0 : slot + 1;
-        cur = nxt;
+    } else {
+        CostConsumer<R> C;
+        const int tid = threadIdx.x - COST_ROLE;
+        for (int i = tid; i < nring; i += COST_ROLE) sts128(C.ring0(t) + 16u * i, 0, 0, 0, 0);
+        bar_sync(COST_BAR_CONS, COST_ROLE);
+        C.init(a, t, tid, b);
+        for (int r = t.r0; r <= t.r1; r++) {
+            const int buf = (r - t.r0) & 1;
+            bar_sync(COST_BAR_FULL + buf, 2 * COST_ROLE);                  // row is in pix[buf]
+            C.row(t, r, buf);
+            if (r + 2 <= t.r1) bar_arrive(COST_BAR_EMPTY + buf, 2 * COST_ROLE);   // a producer will wait for it
+        }
     }
 }
 
-struct CostGeom { int TXP, TX, ntiles, rows_per_seg, nseg; size_t smem; };
+struct CostGeom { int NW, TX, NPART, CPT, NCB, ntiles, rows_per_seg, nseg; size_t smem; };
 static CostGeom cost_geom(const SgbmPlan &pl)
 {
     CostGeom g;
-    const int Gc = pl.Dp / 8, NCB = COST_THREADS / Gc, BS = 2 * pl.R + 1;
-    const size_t budget = 200 * 1024;
-    auto bytes = [&](int txp) { return (size_t)2 * ((size_t)2 * txp * (pl.Dp + 8) + (size_t)BS * (txp - 2 * pl.R) * pl.Dp); };
-    // widest tile whose windows fit the CTA (TXP + 8(G-1) <= threads), whose column blocks fit COST_CPB_MAX and
-    // whose buffers fit shared memory
-    int TXP = std::min(COST_THREADS - 8 * (Gc - 1), NCB * COST_CPB_MAX + 2 * pl.R);
-    TXP = std::min(TXP, pl.W1 + 2 * pl.R);
-    while (TXP > 2 * pl.R + 1 && bytes(TXP) > budget) TXP--;
-    g.TXP = TXP; g.TX = TXP - 2 * pl.R;
-    g.ntiles = (pl.W1 + g.TX - 1) / g.TX;
+    const int Gc = pl.Dp / 8, BS = 2 * pl.R + 1;
+    static const size_t budget_kb = getenv("SVB_COST_SMEM_KB") ? atoi(getenv("SVB_COST_SMEM_KB")) : 226;
+    const size_t budget = budget_kb * 1024;
+    g.NPART = std::max(1, Gc / 8);
+    g.CPT = Gc / g.NPART;
+    auto bytes = [&](int nw) { return (size_t)2 * ((size_t)2 * nw * (pl.Dp + 8) + (size_t)BS * (nw - 2 * pl.R) * pl.Dp); };
+    // widest tile whose windows fit the CTA (phase 1: NW*NPART threads), whose column blocks of COST_CPB_MAX columns
+    // fit it too (phase 2: ceil(TX/8)*G threads) and whose buffers fit shared memory
+    int NW = std::min(COST_ROLE / g.NPART, pl.W1 + 8 * (Gc - 1) + 2 * pl.R);
+    NW = std::min(NW, COST_CPB_MAX * (COST_ROLE / Gc) + 2 * pl.R);
+    while (NW > 2 * pl.R + 1 && bytes(NW) > budget) NW--;
+    g.NW = NW; g.TX = NW - 2 * pl.R;
+    g.NCB = (g.TX + COST_CPB_MAX - 1) / COST_CPB_MAX;
+    g.ntiles = (pl.W1 + 8 * (Gc - 1) + g.TX - 1) / g.TX;
     g.nseg = std::max(1, std::min(8, pl.H / 32));
     g.rows_per_seg = (pl.H + g.nseg - 1) / g.nseg;
     g.nseg = (pl.H + g.rows_per_seg - 1) / g.rows_per_seg;
-    g.smem = bytes(TXP);
+    g.smem = bytes(NW);
     return g;
 }
 
-template <int NPL, int R>
+template <int NPL, int R, int GT>
 static int launch_cost_fused(const SgbmPlan &pl, const CostGeom &g, char *ws, size_t ws_stride, int B, cudaStream_t st)
 {
-    auto kern = k_cost_fused<NPL, R>;
+    auto kern = k_cost_fused<NPL, R, GT, COST_WS != 0>;
     static size_t configured = 0;
     if (g.smem > configured) {
         SVB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g.smem));
         configured = g.smem;
     }
-    const int jb0 = pl.W - 1 - pl.minX1 + pl.p.minDisparity;
-    const uint32_t cpad = (uint32_t)(32767 - pl.p.P2) * 0x10001u;
+    CostArgs a;
+    a.LP = (const uint4 *)(ws + pl.off_lplanes); a.RP = (const int16_t *)(ws + pl.off_rplanes); a.Cv = (int16_t *)(ws + pl.off_C);
+    a.H = pl.H; a.W1 = pl.W1; a.Wr = pl.Wr; a.Dp = pl.Dp; a.D = pl.D; a.G = pl.Dp / 8;
+    a.jb0 = pl.W - 1 - pl.minX1 + pl.p.minDisparity;
+    a.NW = g.NW; a.NPART = g.NPART; a.CPT = g.CPT; a.NCB = g.NCB; a.rows_per_seg = g.rows_per_seg;
+    a.zrow = pl.p.mode == 3 ? pl.H - pl.R : pl.H;
+    a.cpad = (uint32_t)(32767 - pl.p.P2) * 0x10001u;
+    a.ws_stride = ws_stride;
     dim3 grid(g.ntiles, g.nseg, B);
-    kern<<<grid, COST_THREADS, g.smem, st>>>((const uint4 *)(ws + pl.off_lplanes), (const int16_t *)(ws + pl.off_rplanes),
-                                             (int16_t *)(ws + pl.off_C), pl.H, pl.W1, pl.Wr, pl.Dp, pl.D, pl.Dp / 8, jb0,
-                                             g.TXP, g.rows_per_seg, cpad, pl.p.mode == 3 ? pl.H - pl.R : pl.H, ws_stride);
+    kern<<<grid, COST_WS ? 2 * COST_ROLE : COST_ROLE, g.smem, st>>>(a);
     SVB_CUDA_CHECK(cudaGetLastError());
     return SVB_OK;
 }
 
-template <int NPL>
+template <int NPL, int GT>
 static int launch_cost_r(const SgbmPlan &pl, const CostGeom &g, char *ws, size_t ws_stride, int B, cudaStream_t st)
 {
     switch (pl.R) {
-    case 0: return launch_cost_fused<NPL, 0>(pl, g, ws, ws_stride, B, st);
-    case 1: return launch_cost_fused<NPL, 1>(pl, g, ws, ws_stride, B, st);
-    case 2: return launch_cost_fused<NPL, 2>(pl, g, ws, ws_stride, B, st);
-    case 3: return launch_cost_fused<NPL, 3>(pl, g, ws, ws_stride, B, st);
-    case 4: return launch_cost_fused<NPL, 4>(pl, g, ws, ws_stride, B, st);
-    default: return launch_cost_fused<NPL, 5>(pl, g, ws, ws_stride, B, st);
+    case 0: return launch_cost_fused<NPL, 0, GT>(pl, g, ws, ws_stride, B, st);
+    case 1: return launch_cost_fused<NPL, 1, GT>(pl, g, ws, ws_stride, B, st);
+    case 2: return launch_cost_fused<NPL, 2, GT>(pl, g, ws, ws_stride, B, st);
+    case 3: return launch_cost_fused<NPL, 3, GT>(pl, g, ws, ws_stride, B, st);
+    case 4: return launch_cost_fused<NPL, 4, GT>(pl, g, ws, ws_stride, B, st);
+    default: return launch_cost_fused<NPL, 5, GT>(pl, g, ws, ws_stride, B, st);
     }
 }
 
 int svb_launch_cost(const SgbmPlan &pl, char *ws, size_t ws_stride, int B, cudaStream_t st)
 {
     const CostGeom g = cost_geom(pl);
-    SVB_REQUIRE(g.smem <= 227 * 1024, SVB_ERR_UNSUPPORTED, "sgbm: cost tile does not fit shared memory (%zu bytes)", g.smem);
-    return pl.nplanes == 2 ? launch_cost_r<2>(pl, g, ws, ws_stride, B, st) : launch_cost_r<6>(pl, g, ws, ws_stride, B, st);
+    SVB_REQUIRE(g.smem <= 227 * 1024 && g.NW > 2 * pl.R + 1, SVB_ERR_UNSUPPORTED,
+                "sgbm: cost tile does not fit shared memory (%zu bytes)", g.smem);
+    const bool g32 = pl.Dp == 256 && g.CPT == 8;   // the 129..256-disparity case gets compile-time strides
+    if (pl.nplanes == 2) return g32 ? launch_cost_r<2, 32>(pl, g, ws, ws_stride, B, st) : launch_cost_r<2, 0>(pl, g, ws, ws_stride, B, st);
+    return g32 ? launch_cost_r<6, 32>(pl, g, ws, ws_stride, B, st) : launch_cost_r<6, 0>(pl, g, ws, ws_stride, B, st);
 }
