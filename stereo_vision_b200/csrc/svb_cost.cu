@@ -342,7 +342,7 @@ struct CostProducer {
     // the window registers hold ONE channel (gradient + intensity plane) at a time; for 3-channel input the pixel
     // cost accumulates in the thread's own shared-memory cells, and the next chunk's operands load while one computes
     CostWindow<2> cur;
-    CostLeft LA;
+    CostLeft LA, LB;   // left operands of cell pairs, fetched two pairs ahead (also across rows)
     const uint4 *LPt;
     const char *rb0;
     size_t rrow_bytes;
@@ -373,6 +373,7 @@ struct CostProducer {
             const int rc0 = max(0, min(t.H - 1, t.r0));
             load_window<2>(cur, rb0 + (size_t)rc0 * rrow_bytes, arr_bytes);
             load_left(LA, LPt + (size_t)rc0 * NPL * t.W1, t.W1, 0, vmask);
+            load_left(LB, LPt + (size_t)rc0 * NPL * t.W1, t.W1, 2, vmask);
         }
     }
     // writes pix row r into buffer buf; `signal()` runs when the row is complete (before the next operands are fetched)
@@ -384,10 +385,8 @@ struct CostProducer {
 #pragma unroll 1
         for (int ch = 0; ch < NCH; ch++) {
             const bool last = ch + 1 == NCH;
-            if (work) {   // 8 cells in pairs, the left operands two pairs ahead
-                CostLeft LB;
+            if (work) {   // 8 cells in pairs; a pair's operands are always fetched right after a compute block
                 const uint4 *LPx = LPt + ((size_t)rc * NPL + 2 * ch) * t.W1;
-                load_left(LB, LPx, t.W1, 2, vmask);
                 cells2(cur, LA, sts, 0, vmask, ch > 0);
                 load_left(LA, LPx, t.W1, 4, vmask);
                 cells2(cur, LB, sts, 2, vmask, ch > 0);
@@ -400,6 +399,7 @@ struct CostProducer {
                 const int rn = max(0, min(t.H - 1, last ? r + 1 : r)), chn = last ? 0 : ch + 1;
                 load_window<2>(cur, rb0 + (size_t)rn * rrow_bytes + (size_t)(chn * 8) * arr_bytes, arr_bytes);
                 load_left(LA, LPt + ((size_t)rn * NPL + 2 * chn) * t.W1, t.W1, 0, vmask);
+                load_left(LB, LPt + ((size_t)rn * NPL + 2 * chn) * t.W1, t.W1, 2, vmask);
             }
         }
     }
