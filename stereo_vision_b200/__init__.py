@@ -9,5 +9,6 @@ from .api import (  # noqa: F401
 )
 from ._lib import SvbError  # noqa: F401
 from .calib import StereoRig, load_calibration  # noqa: F401
+from .stream import HostPipeline  # noqa: F401
 
 __version__ = "0.1.0"

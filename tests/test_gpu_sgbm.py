@@ -148,3 +148,32 @@ def test_mode_hh4_matches_cv2_golden(sv):
     Rb = torch.from_numpy(np.stack([R] * 3)).cuda()
     out = m.compute_batch(Lb, Rb).cpu().numpy()
     assert all(_sha(out[b]) == full["c3_hh4"] for b in range(3))
+
+
+def test_host_pipeline_matches_compute_batch(sv):
+    """HostPipeline (copies of neighbouring batches overlapped with the matcher) == compute_batch, batch by batch."""
+    import torch
+    H, W, D = 96, 320, 64
+    kw = dict(minDisparity=0, numDisparities=D, blockSize=5, P1=200, P2=800, disp12MaxDiff=1, uniquenessRatio=10,
+              speckleWindowSize=50, speckleRange=2, mode=1)
+    m = sv.StereoSGBM_create(**kw)
+    pipe = sv.HostPipeline(m)
+    Q = np.array([[1, 0, 0, -W / 2], [0, 1, 0, -H / 2], [0, 0, 0, 500.0], [0, 0, 1 / 60.0, 0]])
+    batches, outs, meds = [], [], []
+    boxes = synth.boxes_for_frame(H, W, D, n=4, seed=1)
+    boxes_b = np.concatenate([boxes, boxes]); bi = np.repeat(np.arange(2, dtype=np.int32), 4)
+    for i in range(5):
+        pairs = [synth.stereo_pair(H, W, D, seed=100 + 2 * i + j) for j in range(2)]
+        L = torch.from_numpy(np.stack([p[0] for p in pairs])).pin_memory()
+        R = torch.from_numpy(np.stack([p[1] for p in pairs])).pin_memory()
+        batches.append((L, R))
+        outs.append(torch.empty((2, H, W), dtype=torch.int16).pin_memory())
+        meds.append(torch.empty(8, dtype=torch.float32).pin_memory())
+    for (L, R), o, md in zip(batches, outs, meds):
+        pipe.submit(L, R, o, Q=Q, boxes=boxes_b, box_image=bi, med_h=md)
+    pipe.synchronize()
+    for (L, R), o, md in zip(batches, outs, meds):
+        ref = m.compute_batch(L.cuda(), R.cuda())
+        assert torch.equal(o, ref.cpu())
+        refm = sv.box_median_depth(ref, Q, boxes_b, box_image=bi).cpu().numpy()
+        assert np.array_equal(md.numpy(), refm, equal_nan=True)
