@@ -177,3 +177,28 @@ def test_host_pipeline_matches_compute_batch(sv):
         assert torch.equal(o, ref.cpu())
         refm = sv.box_median_depth(ref, Q, boxes_b, box_image=bi).cpu().numpy()
         assert np.array_equal(md.numpy(), refm, equal_nan=True)
+
+
+def test_geometry_fuzz_vs_oracle(sv):
+    """Cost-tile / sweep geometry corners: every disparity-group count (D = 16 .. 512), widths around tile multiples,
+    all block sizes, 1 and 3 channels, negative / positive minDisparity — GPU vs the CPU oracle, bit-exact."""
+    rng = np.random.default_rng(77)
+    cfgs = [(16, 1), (32, 3), (48, 5), (64, 7), (96, 9), (128, 11), (144, 5), (208, 3), (256, 5), (272, 5), (384, 3), (512, 5)]
+    bad = []
+    for D, bs in cfgs:
+        for rep in range(2):
+            ch = 3 if (rep == 1 and D <= 256) else 1
+            minD = int(rng.choice([0, -16, 8]))
+            H = int(rng.integers(17, 40))
+            W = D + abs(minD) + int(rng.choice([9, 23, 61, 64, 65, 127, 130]))
+            mode = int(rng.choice([0, 1, 3]))
+            kw = dict(minDisparity=minD, numDisparities=D, blockSize=bs, P1=8 * ch * bs * bs, P2=32 * ch * bs * bs,
+                      disp12MaxDiff=1, preFilterCap=31, uniquenessRatio=10, speckleWindowSize=20, speckleRange=2, mode=mode)
+            if bs * bs * ch * (2 * 31 + 63) + kw["P2"] > 32767:
+                continue
+            L, R = synth.stereo_pair(H, W, D, seed=int(rng.integers(1 << 30)), channels=ch)
+            got = sv.StereoSGBM_create(**kw).compute(L, R)
+            ref = oracle.sgbm_compute(L, R, **kw)
+            if not np.array_equal(got, ref):
+                bad.append((D, bs, ch, minD, H, W, mode, int((got != ref).sum())))
+    assert not bad, bad
