@@ -16,6 +16,7 @@ CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(HERE, "_obj")
 SO = os.path.join(HERE, "libsvb.so")
 SOURCES = ["svb_api.cu", "svb_rectify.cu", "svb_cost.cu", "svb_aggregate.cu", "svb_post.cu", "svb_depth.cu", "svb_bench.cu", "svb_sparse.cu"]
+AGG_PARTS = 5
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC",
          "-Xcompiler", "-fvisibility=default", "--threads", "2"]
@@ -30,16 +31,21 @@ def _deps_mtime() -> float:
 def build(force: bool = False, verbose: bool = False) -> str:
     os.makedirs(OBJ, exist_ok=True)
     hm = _deps_mtime()
-    todo = []
+    todo, objs = [], []
     for s in SOURCES:
         src = os.path.join(CSRC, s)
-        obj = os.path.join(OBJ, s[:-3] + ".o")
-        if force or not os.path.exists(obj) or os.path.getmtime(obj) < max(os.path.getmtime(src), hm):
-            todo.append((src, obj))
+        # the sweep kernel families of svb_aggregate.cu are separate objects (they dominate the build time)
+        parts = [(f"_p{k}", [f"-DSVB_AGG_PART={k}"]) for k in range(AGG_PARTS)] if s == "svb_aggregate.cu" else [("", [])]
+        for tag, defs in parts:
+            obj = os.path.join(OBJ, s[:-3] + tag + ".o")
+            objs.append(obj)
+            if force or not os.path.exists(obj) or os.path.getmtime(obj) < max(os.path.getmtime(src), hm):
+                todo.append((src, obj, defs))
+    todo.sort(key=lambda j: 0 if "svb_aggregate" in j[0] else 1)   # longest jobs first
 
     def cc(job):
-        src, obj = job
-        cmd = [NVCC, *FLAGS, "-c", src, "-o", obj] + (["-Xptxas", "-v"] if verbose else [])
+        src, obj, defs = job
+        cmd = [NVCC, *FLAGS, *defs, "-c", src, "-o", obj] + (["-Xptxas", "-v"] if verbose else [])
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             raise RuntimeError(f"nvcc failed for {src}:\n{r.stdout}\n{r.stderr}")
@@ -47,9 +53,8 @@ def build(force: bool = False, verbose: bool = False) -> str:
             sys.stderr.write(r.stderr)
         return obj
 
-    with ThreadPoolExecutor(max_workers=min(6, os.cpu_count() or 1)) as ex:
+    with ThreadPoolExecutor(max_workers=min(8, os.cpu_count() or 1)) as ex:
         list(ex.map(cc, todo))
-    objs = [os.path.join(OBJ, s[:-3] + ".o") for s in SOURCES]
     if todo or not os.path.exists(SO):
         cmd = [NVCC, "-shared", "-o", SO, *objs, "-gencode", "arch=compute_100a,code=sm_100a", "-lcudart"]
         r = subprocess.run(cmd, capture_output=True, text=True)

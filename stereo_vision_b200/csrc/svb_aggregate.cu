@@ -26,11 +26,32 @@
 //     scalar tail (uniqueness test, subpixel division, disp2 scatter, store) runs lane-parallel every G pixels.
 #include "svb_common.cuh"
 
+#ifndef AGG_MIN3
+#define AGG_MIN3 1         // dir_update: one VIMNMX3 per register (0: VIMNMX + VIADDMNMX)
+#endif
+#ifndef AGG_PPS
+#define AGG_PPS 2          // pixels every row advances per CTA barrier
+#endif
+#if AGG_PPS == 2
+#define AGG_LAG 3          // row v trails row v-1 by AGG_LAG pixels (PPS + 1: the u+1 predecessor is one barrier old)
+#define AGG_SLOTS 6        // ring depth: a vector is read up to LAG+1 pixel-times after it was written, i.e. two
+                           // barriers later, and its slot is rewritten SLOTS/PPS barriers later
+#define AGG_ENS 12         // slots of the cross-band "row -1" ring
+#define AGG_EPF 8          // cross-band prefetch distance: at pixel-time t pixels <= t+EPF may be issued; the slot of
+                           // pixel t+EPF holds pixel t+EPF-ENS, which row 0 may still be reading during the previous
+                           // barrier interval unless EPF <= ENS-PPS-2
+#define AGG_UNROLL 12      // pixel-times per loop iteration: a multiple of SLOTS, ENS, PPS and the prefetch depths
+#else
+#define AGG_LAG 2
 #define AGG_SLOTS 4        // ring depth (u-1, u, u+1 live + one being written)
-#define AGG_ENS 8          // slots of the cross-band "row -1" ring
-#define AGG_EPF 5          // cross-band prefetch distance: at step t pixels <= t+EPF may be issued; the slot of pixel
-                           // t+EPF holds pixel t+EPF-ENS, which row 0 may still be reading in step t-1 unless EPF <= ENS-3
+#define AGG_ENS 8
+#define AGG_EPF 5          // <= ENS-3
+#define AGG_UNROLL 8
+#endif
 #define AGG_PUB 8          // publish cross-band progress every AGG_PUB pixels
+#ifndef AGG_L2PF
+#define AGG_L2PF 32        // cross-band L2 prefetch distance (pixels ahead of the cp.async front), 0 = off
+#endif
 #define AGG_PADE 8         // int16 elements of P2 halo in front of every ring vector
 
 #ifdef EXP_HARNESS
@@ -49,6 +70,7 @@ struct AggArgs {
     int nbands, B;
     int flip;              // 0: rows top-down, x ascending; 1: both reversed
     uint32_t P1d, P2d;     // duplicated halves
+    uint32_t one;          // == 1 (an opaque multiplier: x * one + y stays an IMAD on the FMA pipe)
     int uniq, invalid16;
     int slack;             // extra producer lead a starving band waits for (0 when one frame is in flight)
 };
@@ -70,6 +92,10 @@ __device__ __forceinline__ void cp_async16(void *smem, const void *gmem)
 {
     const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void prefetch_l2(const void *gmem)
+{
+    asm volatile("prefetch.global.L2::evict_last [%0];" ::"l"(gmem));
 }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N>
@@ -101,19 +127,29 @@ __device__ __forceinline__ uint32_t lane_min16(const uint32_t (&L)[NR])
 // wnext (lo half = Lc[d0+E]).  Produces L[].
 template <int NR>
 __device__ __forceinline__ void dir_update(const uint32_t (&p)[NR], uint32_t wprev, uint32_t wnext,
-                                           const uint32_t (&c)[NR], uint32_t P1d, uint32_t (&L)[NR])
+                                           const uint32_t (&c)[NR], uint32_t P1d, uint32_t one, uint32_t (&L)[NR])
 {
     uint32_t m[NR + 1];
     m[0] = __byte_perm(wprev, p[0], 0x5432);
 #pragma unroll
     for (int k = 1; k < NR; k++) m[k] = __byte_perm(p[k - 1], p[k], 0x5432);
     m[NR] = __byte_perm(p[NR - 1], wnext, 0x5432);
+#if AGG_MIN3
+    // min(Lc(d), Lc(d-1)+P1, Lc(d+1)+P1) as one three-input packed min: the +P1 of the 5 shifted words is a plain
+    // 32-bit add (Lc <= P2, so no carry between halves; up to 2*P2 <= 65534, hence the unsigned compare) that can
+    // issue on the FMA pipe, and the ALU pipe sees one VIMNMX3 instead of VIMNMX + VIADDMNMX per register.
+#pragma unroll
+    for (int k = 0; k <= NR; k++) m[k] = m[k] * one + P1d;   // 'one' is a kernel argument == 1: keeps it an IMAD
+#pragma unroll
+    for (int k = 0; k < NR; k++) L[k] = c[k] + __vimin3_u16x2(p[k], m[k], m[k + 1]);
+#else
 #pragma unroll
     for (int k = 0; k < NR; k++) {
         const uint32_t nb = __vmins2(m[k], m[k + 1]);
         const uint32_t t = __viaddmin_s16x2(nb, P1d, p[k]);
         L[k] = c[k] + t;   // packed add, no carry: C + t <= 32767 by contract
     }
+#endif
 }
 
 // add L into S, then normalise L in place: Lc = min(L - min_d L, P2) (padded disparities forced to P2)
@@ -235,8 +271,6 @@ struct SweepSmem {
     }
 };
 
-#define AGG_UNROLL 8
-
 // Per-thread state of a compute lane.  All arrays are indexed by compile-time constants only.
 template <int NR, int G, int NGRP, int NV, bool PASS2, bool SAFE, bool PAD, int PFD>
 struct SweepLane {
@@ -291,7 +325,7 @@ struct SweepLane {
             uint32_t wnext = __shfl_down_sync(0xffffffffu, h[0], 1, G);
             if (lane == 0) wprev = P2d;
             if (lane == G - 1) wnext = P2d;
-            dir_update<NR>(h, wprev, wnext, c, P1d, L);
+            dir_update<NR>(h, wprev, wnext, c, P1d, a.one, L);
             finish_dir<NR, G, SAFE, PAD>(L, s, P2d, keep);
 #pragma unroll
             for (int k = 0; k < NR; k++) h[k] = L[k];
@@ -308,17 +342,17 @@ struct SweepLane {
 #pragma unroll
             for (int j = 0; j < 3; j++) {
                 if (NV == 1 && j != 1) continue;   // MODE_HH4: the vertical predecessor only
-                const int offv = (((PH + 1 + j) & (AGG_SLOTS - 1)) * 3 + j) * VS;          // written 3-j steps ago
-                const int offe = (((PH + AGG_ENS - 1 + j) & (AGG_ENS - 1)) * 3 + j) * VS;  // pixel u-1+j, u == t
+                const int offv = (((PH + AGG_SLOTS - 1 - AGG_LAG + j) % AGG_SLOTS) * 3 + j) * VS;   // written LAG+1-j pixel-times ago
+                const int offe = (((PH + AGG_ENS - 1 + j) % AGG_ENS) * 3 + j) * VS;               // pixel u-1+j, u == t
                 const int16_t *src = prevL + (isRow0 ? offe : offv);
                 if (j == 2 && u + 1 >= W1) src = zeroL;
                 uint32_t p[NR];
                 ld_regs_shared<NR>(src, p);
                 const uint32_t wprev = *reinterpret_cast<const uint32_t *>(src - 2);
                 const uint32_t wnext = *reinterpret_cast<const uint32_t *>(src + E);
-                dir_update<NR>(p, wprev, wnext, c, P1d, L);
+                dir_update<NR>(p, wprev, wnext, c, P1d, a.one, L);
                 finish_dir<NR, G, SAFE, PAD>(L, s, P2d, keep);
-                st_regs<NR>(wbase + ((PH & (AGG_SLOTS - 1)) * 3 + j) * VS, L);
+                st_regs<NR>(wbase + ((PH % AGG_SLOTS) * 3 + j) * VS, L);
                 st_regs_cg_pred<NR>(eptr + j * Dp, L, epred);
             }
         }
@@ -426,7 +460,7 @@ __global__ void __launch_bounds__(NGRP *G + (NV ? 32 : 0)) k_sweep(const __grid_
     const size_t edge_band = (size_t)W1 * 3 * Dp;
     int16_t *rowm1 = ring + (size_t)NGRP * AGG_SLOTS * 3 * VS;          // vectors [ENS][3]
     int16_t *zerov = rowm1 + (size_t)AGG_ENS * 3 * VS;
-    const int lag_last = 2 * (NGRP - 1);
+    const int lag_last = AGG_LAG * (NGRP - 1);
     const int nsteps = (W1 + (NV ? lag_last : 0) + AGG_UNROLL - 1) / AGG_UNROLL * AGG_UNROLL;
 
     if (NV && tid >= NCOMP) {
@@ -443,7 +477,7 @@ __global__ void __launch_bounds__(NGRP *G + (NV ? 32 : 0)) k_sweep(const __grid_
 #else
             const int16_t *src = edge_in + (size_t)pe * 3 * Dp;
 #endif
-            int16_t *dst = rowm1 + (size_t)((pe & (AGG_ENS - 1)) * 3) * VS + AGG_PADE;
+            int16_t *dst = rowm1 + (size_t)((pe % AGG_ENS) * 3) * VS + AGG_PADE;
 #ifndef EXP_NOFETCH
 #pragma unroll
             for (int i0 = 0; i0 < NCH; i0 += 32) {
@@ -455,6 +489,18 @@ __global__ void __launch_bounds__(NGRP *G + (NV ? 32 : 0)) k_sweep(const __grid_
         // Non-blocking hand-off: the progress counter is re-read every step with the load issued one step before its
         // value is used; pixels are pulled up to AGG_EPF ahead of row 0 as far as the producer allows (at most two per
         // step when catching up).  Only when the pixel row 0 needs next is not even published does the warp spin.
+        // The edge vectors of a band 20 % of a row behind its producer have left L2 by the time they are needed (the
+        // C/S streams of 148 bands pass through it), and under that load an HBM round trip is longer than the two
+        // steps wait_group leaves a cp.async: pull every pixel's 6*Dp bytes into L2 AGG_L2PF pixels ahead.
+        const int l2lines = (6 * Dp + 127) >> 7;
+        auto l2fetch = [&](int pe) {
+            if (lane < l2lines) prefetch_l2(reinterpret_cast<const char *>(edge_in + (size_t)pe * 3 * Dp) + lane * 128);
+            if (l2lines > 32 && lane + 32 < l2lines)
+                prefetch_l2(reinterpret_cast<const char *>(edge_in + (size_t)pe * 3 * Dp) + (lane + 32) * 128);
+        };
+        int l2pf = consumer ? 0 : W1;
+        if (AGG_L2PF > 0 && consumer)
+            for (; l2pf < min(AGG_L2PF, W1); l2pf++) l2fetch(l2pf);
         unsigned known = consumer ? 0u : (unsigned)W1, pending = 0;
         int fetched = consumer ? 0 : W1;   // pixels [0, fetched) are issued
         int f1 = fetched, f2 = fetched;    // 'fetched' one and two steps ago
@@ -462,11 +508,13 @@ __global__ void __launch_bounds__(NGRP *G + (NV ? 32 : 0)) k_sweep(const __grid_
         known = (unsigned)W1;
 #endif
         if (consumer) pending = ld_acquire(prog_in);
-        for (int t = 0; t < nsteps; t++) {
+        for (int t = 0; t < nsteps; t += AGG_PPS) {
+            // this iteration runs alongside the compute lanes' pixel-times t-PPS..t-1 and prepares t..t+PPS-1,
+            // in which row 0 reads pixels < t+PPS+1
+            const int need = min(t + AGG_PPS + 1, W1);
             if (consumer) {
                 known = max(known, pending);
                 if (known < (unsigned)W1) pending = ld_acquire(prog_in);
-                const int need = min(t + 2, W1);                       // pixels row 0 reads in step t: < t+2
 #ifdef EXP_HARNESS
                 if ((int)known < need && lane == 0) { atomicAdd(&g_spin[0], 1ull); }
                 { long long c0 = clock64();
@@ -480,12 +528,18 @@ __global__ void __launch_bounds__(NGRP *G + (NV ? 32 : 0)) k_sweep(const __grid_
                 if (lane == 0) atomicAdd(&g_spin[2], 1ull);
 #endif
                 const int limit = min(min(t + 1 + AGG_EPF, W1), (int)known);
-                if (fetched < limit) fetch(fetched++);
-                if (fetched < limit) fetch(fetched++);
+#pragma unroll
+                for (int i = 0; i < 2 * AGG_PPS; i++)
+                    if (fetched < limit) fetch(fetched++);
+                if (AGG_L2PF > 0) {
+                    const int l2lim = min(fetched + AGG_L2PF, W1);
+#pragma unroll
+                    for (int i = 0; i < 2 * AGG_PPS; i++)
+                        if (l2pf < l2lim) l2fetch(l2pf++);
+                }
             }
             cp_async_commit();
-            // everything issued up to two steps ago is complete after wait_group<2>; fall back when that is not enough
-            const int need = min(t + 2, W1);
+            // everything issued up to two iterations ago is complete after wait_group<2>; fall back when that is not enough
             if (f2 >= need) cp_async_wait<2>();
             else if (f1 >= need) cp_async_wait<1>();
             else cp_async_wait<0>();
@@ -493,7 +547,7 @@ __global__ void __launch_bounds__(NGRP *G + (NV ? 32 : 0)) k_sweep(const __grid_
             cta_barrier();
             if (producer && lane == 0) {
                 const int done = t - lag_last;   // pixels of the last row finished before this barrier
-                if (done > 0 && done < W1 && (done % AGG_PUB) == 0) st_release(prog + band, (unsigned)done);
+                if (done > 0 && done < W1 && (done % AGG_PUB) < AGG_PPS) st_release(prog + band, (unsigned)done);
             }
         }
         cta_barrier();
@@ -506,7 +560,7 @@ __global__ void __launch_bounds__(NGRP *G + (NV ? 32 : 0)) k_sweep(const __grid_
     const int g = tid / G, lane = tid % G;
     const int v = band * NGRP + g;
     st.W1 = W1; st.Dp = Dp; st.VS = VS; st.lane = lane;
-    st.lag = NV ? 2 * g : 0;
+    st.lag = NV ? AGG_LAG * g : 0;
     st.rowActive = v < a.H;
     st.isRow0 = (g == 0);
     st.y = a.flip ? a.H - 1 - v : v;
@@ -538,10 +592,13 @@ __global__ void __launch_bounds__(NGRP *G + (NV ? 32 : 0)) k_sweep(const __grid_
     if (PFD > 1) st.template prefetch_s<(PFD > 1 ? 1 : 0)>(1 - st.lag);
 
     for (int t0 = 0; t0 < nsteps; t0 += AGG_UNROLL) {
-#define SVB_STEP(PH)                 \
-    if (NV) cta_barrier();           \
+#define SVB_STEP(PH)                                   \
+    if (NV && (PH) % AGG_PPS == 0) cta_barrier();      \
     st.template step<PH>(a, t0 + PH, dpre, keys);
         SVB_STEP(0) SVB_STEP(1) SVB_STEP(2) SVB_STEP(3) SVB_STEP(4) SVB_STEP(5) SVB_STEP(6) SVB_STEP(7)
+#if AGG_UNROLL == 12
+        SVB_STEP(8) SVB_STEP(9) SVB_STEP(10) SVB_STEP(11)
+#endif
 #undef SVB_STEP
     }
     if (NV) cta_barrier();
@@ -586,6 +643,39 @@ static int launch_sweep(int safe, int pad, int NR, int G, const AggArgs &a, int 
                : launch_sweep_g<NV, PASS2, false, false>(NR, G, a, ngrid, st);
 }
 
+// The five (NV, PASS2) families are compiled as separate translation units (build.py: -DSVB_AGG_PART=0..4) so that
+// the 120 kernel instantiations build in parallel; without the define everything lands in one object.
+#ifndef SVB_AGG_PART
+#define SVB_AGG_PART -1
+#endif
+#ifndef EXP_HARNESS
+#define SVB_SWEEP_DEF(NAME, NV, PASS2)                                                                       \
+    int NAME(int safe, int pad, int NR, int G, const AggArgs &a, int ngrid, cudaStream_t st)                 \
+    {                                                                                                        \
+        return launch_sweep<NV, PASS2>(safe, pad, NR, G, a, ngrid, st);                                      \
+    }
+int svb_sweep_nv3_p1(int safe, int pad, int NR, int G, const AggArgs &a, int ngrid, cudaStream_t st);
+int svb_sweep_nv3_p2(int safe, int pad, int NR, int G, const AggArgs &a, int ngrid, cudaStream_t st);
+int svb_sweep_nv1_p1(int safe, int pad, int NR, int G, const AggArgs &a, int ngrid, cudaStream_t st);
+int svb_sweep_nv1_p2(int safe, int pad, int NR, int G, const AggArgs &a, int ngrid, cudaStream_t st);
+int svb_sweep_nv0_p2(int safe, int pad, int NR, int G, const AggArgs &a, int ngrid, cudaStream_t st);
+#if SVB_AGG_PART == -1 || SVB_AGG_PART == 0
+SVB_SWEEP_DEF(svb_sweep_nv3_p1, 3, false)
+#endif
+#if SVB_AGG_PART == -1 || SVB_AGG_PART == 1
+SVB_SWEEP_DEF(svb_sweep_nv3_p2, 3, true)
+#endif
+#if SVB_AGG_PART == -1 || SVB_AGG_PART == 2
+SVB_SWEEP_DEF(svb_sweep_nv1_p1, 1, false)
+#endif
+#if SVB_AGG_PART == -1 || SVB_AGG_PART == 3
+SVB_SWEEP_DEF(svb_sweep_nv1_p2, 1, true)
+#endif
+#if SVB_AGG_PART == -1 || SVB_AGG_PART == 4
+SVB_SWEEP_DEF(svb_sweep_nv0_p2, 0, true)
+#endif
+
+#if SVB_AGG_PART == -1 || SVB_AGG_PART == 4
 int svb_launch_aggregate(svb_context *ctx, const SgbmPlan &pl, char *ws, size_t ws_stride, int B, int passes,
                          cudaStream_t st)
 {
@@ -608,6 +698,7 @@ int svb_launch_aggregate(svb_context *ctx, const SgbmPlan &pl, char *ws, size_t 
     a.nbands = pl.nbands; a.B = B;
     a.P1d = (uint32_t)pl.p.P1 * 0x10001u;
     a.P2d = (uint32_t)pl.p.P2 * 0x10001u;
+    a.one = 1;
     a.uniq = pl.p.uniquenessRatio;
     a.invalid16 = pl.invalid16;
     a.slack = B > 1 ? 16 : 0;
@@ -620,17 +711,19 @@ int svb_launch_aggregate(svb_context *ctx, const SgbmPlan &pl, char *ws, size_t 
     int rc = SVB_OK;
     const bool hh4 = pl.p.mode == 3;   // left + up, then right + down
     if (passes & 1)
-        rc = hh4 ? launch_sweep<1, false>(pl.safe, pad, NR, pl.G, a, pl.nbands * B, st)
-                 : launch_sweep<3, false>(pl.safe, pad, NR, pl.G, a, pl.nbands * B, st);
+        rc = hh4 ? svb_sweep_nv1_p1(pl.safe, pad, NR, pl.G, a, pl.nbands * B, st)
+                 : svb_sweep_nv3_p1(pl.safe, pad, NR, pl.G, a, pl.nbands * B, st);
     if (rc || !(passes & 2)) return rc;
     a.flip = 1;
     if (pl.p.mode == 1 || hh4) {   // MODE_HH: right, down-right, down, down-left + selection; MODE_HH4: right, down
         a.prog = (unsigned *)(ws + pl.off_prog) + pl.nbands;
         a.ticket = ctx->tickets + 1;
-        rc = hh4 ? launch_sweep<1, true>(pl.safe, pad, NR, pl.G, a, pl.nbands * B, st)
-                 : launch_sweep<3, true>(pl.safe, pad, NR, pl.G, a, pl.nbands * B, st);
+        rc = hh4 ? svb_sweep_nv1_p2(pl.safe, pad, NR, pl.G, a, pl.nbands * B, st)
+                 : svb_sweep_nv3_p2(pl.safe, pad, NR, pl.G, a, pl.nbands * B, st);
     } else {                // MODE_SGBM: 5th path (from the right) + selection, rows independent
-        rc = launch_sweep<0, true>(pl.safe, pad, NR, pl.G, a, pl.nbands * B, st);
+        rc = svb_sweep_nv0_p2(pl.safe, pad, NR, pl.G, a, pl.nbands * B, st);
     }
     return rc;
 }
+#endif   // SVB_AGG_PART (host dispatch lives in part 4)
+#endif   // !EXP_HARNESS
