@@ -265,9 +265,11 @@ struct SweepSmem {
     __host__ __device__ static int ring_elems(int Dp) { return NV ? nvec() * vs(Dp) + AGG_PADE : 0; }
     __host__ __device__ static int scratch_elems(int Dp) { return PASS2 ? NGRP * 2 * Dp : 0; }
     __host__ __device__ static int mask_elems(int E) { return PASS2 ? (E + 4) * E : 0; }
+    // pass 2: per row, 2*AGG_UNROLL parked pixels x (best key, second-best S, subpixel taps, -) as uint4
+    __host__ __device__ static int park_elems() { return PASS2 ? NGRP * 2 * AGG_UNROLL * 8 : 0; }
     __host__ __device__ static size_t bytes(int Dp, int E)
     {
-        return 2 * (size_t)(ring_elems(Dp) + scratch_elems(Dp) + mask_elems(E)) + 16;
+        return 2 * (size_t)(ring_elems(Dp) + scratch_elems(Dp) + mask_elems(E) + park_elems()) + 16;
     }
 };
 
@@ -275,35 +277,45 @@ struct SweepSmem {
 template <int NR, int G, int NGRP, int NV, bool PASS2, bool SAFE, bool PAD, int PFD>
 struct SweepLane {
     static constexpr int E = 2 * NR;
+    static constexpr int DP = G * E;                // padded disparities of this instantiation (== a.Dp)
+    static constexpr int XDIR = PASS2 ? -1 : 1;     // pass 2 walks every row right to left (and the rows bottom-up)
     // loop-invariant
-    int W1, Dp, VS, lag, lane, y, xdir, xbase;      // x = xbase + xdir*u
+    int W1, VS, lag, lane, y, xbase;                // x = xbase + XDIR*u
     bool rowActive, isRow0;
     uint32_t P1d, P2d;
     uint32_t keep[NR];
-    const int16_t *Crow;        // + lane*E, row y
-    int16_t *Srow;
     const int16_t *prevL;       // ring vectors of row g-1 (data start + lane*E); rowm1 ring for g == 0
     int16_t *ownL;              // ring vectors of row g
     const int16_t *zeroL;
     int16_t *trashL;            // ring-shaped scratch row: where inactive steps park their (meaningless) vectors
-    int16_t *edge_out;          // + lane*E, or nullptr
+    bool edgeRow;               // last row of a band that has a successor
     int16_t *scratch;           // pass 2: 2*Dp per group
     const int16_t *masktab;
-    // loop-carried
+    uint4 *park;                // pass 2: this row's parked pixels
+    // loop-carried.  The three streams are addressed as (pointer of pixel-time t0) + compile-time offset: the pointers
+    // move once per unrolled iteration and are NOT clamped to the row — prefetches of the ramp-up / ramp-down
+    // pixel-times read up to (lag_last + AGG_UNROLL + PFD) vectors outside it (values never used; the workspace keeps a
+    // margin of SVB_SWEEP_MARGIN bytes around C and S), stores are predicated.
+    const int16_t *cptr;        // C  of pixel u = t0 - lag, + lane*E
+    int16_t *sptr;              // S  likewise
+    int16_t *eptr;              // edge_out vector 0 of pixel u = t0 - lag, + lane*E
+    uint4 *parkw;               // park slot of pixel-time t0 (toggles between the two halves)
     uint32_t h[NR];
     static constexpr int PFS = PFD > 2 ? 2 : PFD;   // S (pass 2) is prefetched less deep than C: it is consumed at the
                                                     // end of the step, and its registers are what pass 2 is short of
     uint32_t cbuf[PFD][NR], sbuf[PFS][NR];
-    uint32_t cap_best, cap_s2, cap_taps;
 
-    __device__ __forceinline__ size_t pix_off(int upf) const
+    template <int SLOT, int OFF>   // pixel u = t0 - lag + OFF
+    __device__ __forceinline__ void prefetch_c() { ld_regs_stream<NR>(cptr + XDIR * OFF * DP, cbuf[SLOT]); }
+    template <int SLOT, int OFF>
+    __device__ __forceinline__ void prefetch_s() { if (PASS2) ld_regs_stream<NR>(sptr + XDIR * OFF * DP, sbuf[SLOT]); }
+    __device__ __forceinline__ void advance()
     {
-        return (size_t)(xbase + xdir * min(max(upf, 0), W1 - 1)) * Dp;
+        cptr += XDIR * AGG_UNROLL * DP;
+        sptr += XDIR * AGG_UNROLL * DP;
+        eptr += AGG_UNROLL * 3 * DP;
+        if (PASS2) parkw = park + ((parkw - park) ^ AGG_UNROLL);
     }
-    template <int SLOT>
-    __device__ __forceinline__ void prefetch_c(int upf) { ld_regs_stream<NR>(Crow + pix_off(upf), cbuf[SLOT]); }
-    template <int SLOT>
-    __device__ __forceinline__ void prefetch_s(int upf) { if (PASS2) ld_regs_stream<NR>(Srow + pix_off(upf), sbuf[SLOT]); }
 
     template <int PH>
     __device__ __forceinline__ void step(const AggArgs &a, int t, int16_t *dpre, unsigned *keys)
@@ -314,8 +326,8 @@ struct SweepLane {
         uint32_t c[NR], s[NR], L[NR];
 #pragma unroll
         for (int k = 0; k < NR; k++) { c[k] = cbuf[PB][k]; s[k] = (PASS2 && !SAFE) ? sbuf[PH % PFS][k] : 0u; }
-        prefetch_c<PB>(u + PFD);
-        if (!SAFE) prefetch_s<PH % PFS>(u + PFS);
+        prefetch_c<PB, PH + PFD>();
+        if (!SAFE) prefetch_s<PH % PFS, PH + PFS>();
         // ---- horizontal path (registers) ----
         {
             const uint32_t hm = u > 0 ? 0xFFFFFFFFu : 0u;
@@ -336,9 +348,8 @@ struct SweepLane {
 #ifdef EXP_NOEDGEST
             const bool epred = false;
 #else
-            const bool epred = act && edge_out != nullptr;
+            const bool epred = act && edgeRow;
 #endif
-            int16_t *eptr = edge_out + (size_t)(act ? u : 0) * 3 * Dp;
 #pragma unroll
             for (int j = 0; j < 3; j++) {
                 if (NV == 1 && j != 1) continue;   // MODE_HH4: the vertical predecessor only
@@ -353,7 +364,7 @@ struct SweepLane {
                 dir_update<NR>(p, wprev, wnext, c, P1d, a.one, L);
                 finish_dir<NR, G, SAFE, PAD>(L, s, P2d, keep);
                 st_regs<NR>(wbase + ((PH % AGG_SLOTS) * 3 + j) * VS, L);
-                st_regs_cg_pred<NR>(eptr + j * Dp, L, epred);
+                st_regs_cg_pred<NR>(eptr + (PH * 3 + j) * DP, L, epred);
             }
         }
         if (!PASS2) {
@@ -361,12 +372,12 @@ struct SweepLane {
 #pragma unroll
                 for (int k = 0; k < NR; k++) s[k] = __vminu2(s[k], 0x7FFF7FFFu);
             }
-            st_regs_cs_pred<NR>(Srow + (size_t)(xbase + xdir * (act ? u : 0)) * Dp, s, act);
+            st_regs_cs_pred<NR>(sptr + XDIR * PH * DP, s, act);
         } else {
             if (SAFE) {   // pass-1 S joins last (plain packed adds commute): its load has the whole step to land
 #pragma unroll
                 for (int k = 0; k < NR; k++) s[k] += sbuf[PH % PFS][k];
-                prefetch_s<PH % PFS>(u + PFS);
+                prefetch_s<PH % PFS, PH + PFS>();
             }
 #pragma unroll
             for (int k = 0; k < NR; k++) {
@@ -394,17 +405,29 @@ struct SweepLane {
                 s2 = group_min_u32<G>(lane_min16<NR>(sm));
             }
             // subpixel taps through shared memory (double-buffered per group)
-            int16_t *sc = scratch + (PH & 1) * Dp;
+            int16_t *sc = scratch + (PH & 1) * DP;
             st_regs<NR>(sc + lane * E, s);
             __syncwarp();
             const uint32_t sm1 = (uint16_t)sc[max(bestD - 1, 0)];
-            const uint32_t sp1 = (uint16_t)sc[min(bestD + 1, Dp - 1)];
-            if (lane == (u & (G - 1))) { cap_best = best; cap_s2 = s2; cap_taps = sm1 | (sp1 << 16); }
-            if (act && ((u & (G - 1)) == G - 1 || u == W1 - 1)) {
-                const int ul = (u & ~(G - 1)) + lane;
-                if (ul <= u) select_flush(a, dpre, keys, y, xbase + xdir * ul + a.minX1, cap_best, cap_s2, cap_taps);
+            const uint32_t sp1 = (uint16_t)sc[min(bestD + 1, DP - 1)];
+            // park the pixel's scalars (all group-uniform); the scalar tail runs lane-parallel in flush()
+            if (lane == 0) parkw[PH] = make_uint4(best, s2, sm1 | (sp1 << 16), 0u);
+        }
+    }
+
+    // pass 2, end of an unrolled iteration: uniqueness test, subpixel interpolation, disp2 scatter and store of the
+    // pixels parked since the last flush, one pixel per lane (pixel-times tau0 .. tau0+n-1 sit in park slots sl0 ..)
+    __device__ __forceinline__ void flush(const AggArgs &a, int16_t *dpre, unsigned *keys, int tau0, int sl0, int n)
+    {
+        __syncwarp();
+        for (int i = lane; i < n; i += G) {
+            const int u = tau0 + i - lag;
+            if (rowActive && (unsigned)u < (unsigned)W1) {
+                const uint4 q = park[sl0 + i];
+                select_flush(a, dpre, keys, y, xbase + XDIR * u + a.minX1, q.x, q.y, q.z);
             }
         }
+        __syncwarp();
     }
 };
 
@@ -428,6 +451,7 @@ __global__ void __launch_bounds__(NGRP *G + (NV ? 32 : 0)) k_sweep(const __grid_
     int16_t *ring = reinterpret_cast<int16_t *>(smem_raw);
     int16_t *scratch_base = ring + SM::ring_elems(Dp);
     int16_t *masktab = scratch_base + SM::scratch_elems(Dp);
+    int16_t *park_base = masktab + SM::mask_elems(E);   // 16-byte aligned: every region is a multiple of 8 elements
     __shared__ unsigned s_ticket;
     const int tid = threadIdx.x;
     unsigned ticket = blockIdx.x;
@@ -559,37 +583,41 @@ __global__ void __launch_bounds__(NGRP *G + (NV ? 32 : 0)) k_sweep(const __grid_
     SweepLane<NR, G, NGRP, NV, PASS2, SAFE, PAD, PFD> st;
     const int g = tid / G, lane = tid % G;
     const int v = band * NGRP + g;
-    st.W1 = W1; st.Dp = Dp; st.VS = VS; st.lane = lane;
+    typedef SweepLane<NR, G, NGRP, NV, PASS2, SAFE, PAD, PFD> Lane;
+    st.W1 = W1; st.VS = VS; st.lane = lane;
     st.lag = NV ? AGG_LAG * g : 0;
     st.rowActive = v < a.H;
     st.isRow0 = (g == 0);
-    st.y = a.flip ? a.H - 1 - v : v;
-    st.xdir = a.flip ? -1 : 1;
-    st.xbase = a.flip ? W1 - 1 : 0;
+    st.y = PASS2 ? a.H - 1 - v : v;          // pass 2 runs on the image rotated by 180 degrees (a.flip == PASS2)
+    st.xbase = PASS2 ? W1 - 1 : 0;
     st.P1d = a.P1d; st.P2d = a.P2d;
 #pragma unroll
     for (int k = 0; k < NR; k++)
         st.keep[k] = ((lane * E + 2 * k < a.D) ? 0x0000FFFFu : 0u) | ((lane * E + 2 * k + 1 < a.D) ? 0xFFFF0000u : 0u);
-    const size_t rowoff = (size_t)(st.rowActive ? st.y : 0) * W1 * Dp + lane * E;
-    st.Crow = Cv + rowoff;
-    st.Srow = Sv + rowoff;
+    {
+        const ptrdiff_t rowoff = (ptrdiff_t)(st.rowActive ? st.y : 0) * W1 * Dp + lane * E;
+        const ptrdiff_t pix0 = (ptrdiff_t)(st.xbase - Lane::XDIR * st.lag) * Dp;   // pixel u = -lag (pixel-time 0)
+        st.cptr = Cv + rowoff + pix0;
+        st.sptr = Sv + rowoff + pix0;
+        st.eptr = edge + (ptrdiff_t)band * edge_band - (ptrdiff_t)st.lag * 3 * Dp + lane * E;
+    }
     st.ownL = ring + (size_t)(g * AGG_SLOTS * 3) * VS + AGG_PADE + lane * E;
     st.prevL = (g == 0 ? rowm1 : ring + (size_t)((g - 1) * AGG_SLOTS * 3) * VS) + AGG_PADE + lane * E;
     st.zeroL = zerov + AGG_PADE + lane * E;
     st.trashL = zerov + VS + AGG_PADE + lane * E;
-    st.edge_out = (NV && band + 1 < a.nbands && g == NGRP - 1) ? edge + (size_t)band * edge_band + lane * E : nullptr;
+    st.edgeRow = NV && band + 1 < a.nbands && g == NGRP - 1;
     st.scratch = scratch_base + (size_t)g * 2 * Dp;
     st.masktab = masktab;
-    st.cap_best = 0; st.cap_s2 = 0; st.cap_taps = 0;
+    st.park = reinterpret_cast<uint4 *>(park_base) + g * 2 * AGG_UNROLL;
+    st.parkw = st.park;
 #pragma unroll
     for (int k = 0; k < NR; k++) st.h[k] = 0;
-#pragma unroll
-    st.template prefetch_c<0>(0 - st.lag);
-    if (PFD > 1) st.template prefetch_c<(1 < PFD ? 1 : 0)>(1 - st.lag);
-    if (PFD > 2) st.template prefetch_c<(2 < PFD ? 2 : 0)>(2 - st.lag);
-    if (PFD > 3) st.template prefetch_c<(3 < PFD ? 3 : 0)>(3 - st.lag);
-    st.template prefetch_s<0>(0 - st.lag);
-    if (PFD > 1) st.template prefetch_s<(PFD > 1 ? 1 : 0)>(1 - st.lag);
+    st.template prefetch_c<0, 0>();
+    if (PFD > 1) st.template prefetch_c<(1 < PFD ? 1 : 0), 1>();
+    if (PFD > 2) st.template prefetch_c<(2 < PFD ? 2 : 0), 2>();
+    if (PFD > 3) st.template prefetch_c<(3 < PFD ? 3 : 0), 3>();
+    st.template prefetch_s<0, 0>();
+    if (PFD > 1) st.template prefetch_s<(PFD > 1 ? 1 : 0), 1>();
 
     for (int t0 = 0; t0 < nsteps; t0 += AGG_UNROLL) {
 #define SVB_STEP(PH)                                   \
@@ -600,6 +628,12 @@ __global__ void __launch_bounds__(NGRP *G + (NV ? 32 : 0)) k_sweep(const __grid_
         SVB_STEP(8) SVB_STEP(9) SVB_STEP(10) SVB_STEP(11)
 #endif
 #undef SVB_STEP
+        st.advance();
+        if (PASS2) {   // every second iteration (and after the last one) the parked pixels get their scalar tail
+            const bool odd = (t0 / AGG_UNROLL) & 1;
+            if (odd) st.flush(a, dpre, keys, t0 - AGG_UNROLL, 0, 2 * AGG_UNROLL);
+            else if (t0 + AGG_UNROLL >= nsteps) st.flush(a, dpre, keys, t0, 0, AGG_UNROLL);
+        }
     }
     if (NV) cta_barrier();
 }

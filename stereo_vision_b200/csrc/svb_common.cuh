@@ -64,6 +64,9 @@ struct SgbmPlan {
     int Wr;              // right-plane row length (elements) incl. padding
 };
 
+// unclamped prefetch reach of k_sweep around the C / S volumes: (lag_last + AGG_UNROLL + PFD) * Dp * 2 bytes <= 62 KB
+#define SVB_SWEEP_MARGIN (64 << 10)
+
 int svb_make_plan(const svb_sgbm_params *raw, int H, int W, int ch, SgbmPlan *plan);
 
 static inline size_t svb_align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }

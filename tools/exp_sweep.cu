@@ -18,7 +18,8 @@ int main(int argc, char **argv)
     for (int b = 1; b < B; b++) cudaMemcpy(ws + b * stride, ws, vol, cudaMemcpyDeviceToDevice);
     unsigned *tick; cudaMalloc(&tick, 64);
     AggArgs a; memset(&a, 0, sizeof a);
-    a.C = (int16_t *)ws; a.S = (int16_t *)(ws + vol); a.edge = (int16_t *)(ws + 2 * vol);
+    a.C = (int16_t *)ws; a.S = (int16_t *)(ws + vol);
+    a.edge = (int16_t *)(ws + 2 * vol);
     a.prog = (unsigned *)(ws + 2 * vol + edge); a.dpre = (int16_t *)(ws + 2 * vol + edge + 4096);
     a.keys = (unsigned *)(ws + 2 * vol + edge + 4096 + (size_t)H * W * 2);
     a.ws_stride = (argc > 4 && atoi(argv[4])) ? 0 : stride;   // hot: every frame aliases frame 0 (L2-resident)
