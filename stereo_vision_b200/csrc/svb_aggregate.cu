@@ -25,9 +25,13 @@
 //     the per-pixel scalars (min S, best d, second-best S, subpixel taps) are parked one pixel per lane and the
 //     scalar tail (uniqueness test, subpixel division, disp2 scatter, store) runs lane-parallel every G pixels.
 #include "svb_common.cuh"
+#include <stdlib.h>
 
 #ifndef AGG_MIN3
 #define AGG_MIN3 1         // dir_update: one VIMNMX3 per register (0: VIMNMX + VIADDMNMX)
+#endif
+#ifndef AGG_SELPIPE
+#define AGG_SELPIPE 1      // pass 2: the selection of a pixel runs during the next pixel's path updates
 #endif
 #ifndef AGG_PPS
 #define AGG_PPS 2          // pixels every row advances per CTA barrier
@@ -48,7 +52,10 @@
 #define AGG_EPF 5          // <= ENS-3
 #define AGG_UNROLL 8
 #endif
-#define AGG_PUB 8          // publish cross-band progress every AGG_PUB pixels
+#ifndef AGG_PUB
+#define AGG_PUB 8
+#endif
+//          // publish cross-band progress every AGG_PUB pixels
 #ifndef AGG_L2PF
 #define AGG_L2PF 32        // cross-band L2 prefetch distance (pixels ahead of the cp.async front), 0 = off
 #endif
@@ -324,6 +331,10 @@ struct SweepLane {
         const int u = t - lag;
         const bool act = rowActive && (unsigned)u < (unsigned)W1;
         uint32_t c[NR], s[NR], L[NR];
+#if AGG_SELPIPE
+        if (PASS2)   // selection of pixel-time t-1 (slot PH-1 of this half, or the last slot of the other half)
+            select<(PH + AGG_UNROLL - 1) % AGG_UNROLL>(PH ? parkw + (PH - 1) : park + (((parkw - park) ^ AGG_UNROLL) + AGG_UNROLL - 1));
+#endif
 #pragma unroll
         for (int k = 0; k < NR; k++) { c[k] = cbuf[PB][k]; s[k] = (PASS2 && !SAFE) ? sbuf[PH % PFS][k] : 0u; }
         prefetch_c<PB, PH + PFD>();
@@ -384,46 +395,60 @@ struct SweepLane {
                 if (PAD) s[k] |= 0x7FFF7FFFu & ~keep[k];
                 s[k] = __vminu2(s[k], 0x7FFF7FFFu);
             }
-            // winner: first d attaining min S  (key = S<<16 | d)
-            const uint32_t d0 = (uint32_t)lane * E;
-            uint32_t lk = 0xFFFFFFFFu;
-#pragma unroll
-            for (int k = 0; k < NR; k++) {
-                lk = min(lk, __byte_perm(s[k], d0 + 2 * k, 0x1054));       // (S_lo << 16) | d
-                lk = min(lk, __byte_perm(s[k], d0 + 2 * k + 1, 0x3254));   // (S_hi << 16) | d
-            }
-            const uint32_t best = group_min_u32<G>(lk);
-            const int bestD = (int)(best & 0xFFFFu);
-            // second-best S outside bestD-1..bestD+1 (mask table indexed by bestD relative to this lane)
-            uint32_t s2;
-            {
-                const int ti = min(max(bestD - (int)d0 + 2, 0), E + 3);
-                uint32_t mk[NR], sm[NR];
-                ld_regs_shared<NR>(masktab + ti * E, mk);
-#pragma unroll
-                for (int k = 0; k < NR; k++) sm[k] = s[k] | mk[k];
-                s2 = group_min_u32<G>(lane_min16<NR>(sm));
-            }
-            // subpixel taps through shared memory (double-buffered per group)
-            int16_t *sc = scratch + (PH & 1) * DP;
-            st_regs<NR>(sc + lane * E, s);
-            __syncwarp();
-            const uint32_t sm1 = (uint16_t)sc[max(bestD - 1, 0)];
-            const uint32_t sp1 = (uint16_t)sc[min(bestD + 1, DP - 1)];
-            // park the pixel's scalars (all group-uniform); the scalar tail runs lane-parallel in flush()
-            if (lane == 0) parkw[PH] = make_uint4(best, s2, sm1 | (sp1 << 16), 0u);
+#if AGG_SELPIPE
+            // the selection of this pixel runs one pixel-time later (select<>), interleaved with the next pixel's paths
+            st_regs<NR>(scratch + (PH & 1) * DP + lane * E, s);
+#else
+            st_regs<NR>(scratch + (PH & 1) * DP + lane * E, s);
+            select<PH>(parkw + PH);
+#endif
         }
     }
 
-    // pass 2, end of an unrolled iteration: uniqueness test, subpixel interpolation, disp2 scatter and store of the
-    // pixels parked since the last flush, one pixel per lane (pixel-times tau0 .. tau0+n-1 sit in park slots sl0 ..)
-    __device__ __forceinline__ void flush(const AggArgs &a, int16_t *dpre, unsigned *keys, int tau0, int sl0, int n)
+    // pass 2: winner / second best / subpixel taps of the pixel whose clamped S sits in scratch half PHP & 1
+    template <int PHP>
+    __device__ __forceinline__ void select(uint4 *dst)
+    {
+        const int16_t *sc = scratch + (PHP & 1) * DP;
+        __syncwarp();
+        uint32_t s[NR];
+        ld_regs_shared<NR>(sc + lane * E, s);
+        // winner: first d attaining min S  (key = S<<16 | d)
+        const uint32_t d0 = (uint32_t)lane * E;
+        uint32_t lk = 0xFFFFFFFFu;
+#pragma unroll
+        for (int k = 0; k < NR; k++) {
+            lk = min(lk, __byte_perm(s[k], d0 + 2 * k, 0x1054));       // (S_lo << 16) | d
+            lk = min(lk, __byte_perm(s[k], d0 + 2 * k + 1, 0x3254));   // (S_hi << 16) | d
+        }
+        const uint32_t best = group_min_u32<G>(lk);
+        const int bestD = (int)(best & 0xFFFFu);
+        // second-best S outside bestD-1..bestD+1 (mask table indexed by bestD relative to this lane)
+        uint32_t s2;
+        {
+            const int ti = min(max(bestD - (int)d0 + 2, 0), E + 3);
+            uint32_t mk[NR], sm[NR];
+            ld_regs_shared<NR>(masktab + ti * E, mk);
+#pragma unroll
+            for (int k = 0; k < NR; k++) sm[k] = s[k] | mk[k];
+            s2 = group_min_u32<G>(lane_min16<NR>(sm));
+        }
+        // subpixel taps
+        const uint32_t sm1 = (uint16_t)sc[max(bestD - 1, 0)];
+        const uint32_t sp1 = (uint16_t)sc[min(bestD + 1, DP - 1)];
+        // park the pixel's scalars (all group-uniform); the scalar tail runs lane-parallel in flush()
+        if (lane == 0) *dst = make_uint4(best, s2, sm1 | (sp1 << 16), 0u);
+    }
+
+    // pass 2: uniqueness test, subpixel interpolation, disp2 scatter and store of the pixels parked since the last
+    // flush, one pixel per lane: pixel-times tau0 .. tau0+n-1 (park slot = pixel-time mod 2*AGG_UNROLL)
+    __device__ __forceinline__ void flush(const AggArgs &a, int16_t *dpre, unsigned *keys, int tau0, int n)
     {
         __syncwarp();
         for (int i = lane; i < n; i += G) {
-            const int u = tau0 + i - lag;
+            const int tau = tau0 + i, u = tau - lag;
             if (rowActive && (unsigned)u < (unsigned)W1) {
-                const uint4 q = park[sl0 + i];
+                const uint4 q = park[tau % (2 * AGG_UNROLL)];
                 select_flush(a, dpre, keys, y, xbase + XDIR * u + a.minX1, q.x, q.y, q.z);
             }
         }
@@ -619,6 +644,7 @@ __global__ void __launch_bounds__(NGRP *G + (NV ? 32 : 0)) k_sweep(const __grid_
     st.template prefetch_s<0, 0>();
     if (PFD > 1) st.template prefetch_s<(PFD > 1 ? 1 : 0), 1>();
 
+    int ftau = 0;   // pass 2: first pixel-time not flushed yet
     for (int t0 = 0; t0 < nsteps; t0 += AGG_UNROLL) {
 #define SVB_STEP(PH)                                   \
     if (NV && (PH) % AGG_PPS == 0) cta_barrier();      \
@@ -629,11 +655,17 @@ __global__ void __launch_bounds__(NGRP *G + (NV ? 32 : 0)) k_sweep(const __grid_
 #endif
 #undef SVB_STEP
         st.advance();
-        if (PASS2) {   // every second iteration (and after the last one) the parked pixels get their scalar tail
-            const bool odd = (t0 / AGG_UNROLL) & 1;
-            if (odd) st.flush(a, dpre, keys, t0 - AGG_UNROLL, 0, 2 * AGG_UNROLL);
-            else if (t0 + AGG_UNROLL >= nsteps) st.flush(a, dpre, keys, t0, 0, AGG_UNROLL);
+        if (PASS2 && ((t0 / AGG_UNROLL) & 1)) {   // every second iteration the parked pixels get their scalar tail
+            const int upto = t0 + AGG_UNROLL - AGG_SELPIPE;   // pixel-times < upto are parked
+            st.flush(a, dpre, keys, ftau, upto - ftau);
+            ftau = upto;
         }
+    }
+    if (PASS2) {
+#if AGG_SELPIPE
+        st.template select<AGG_UNROLL - 1>(st.park + (((st.parkw - st.park) ^ AGG_UNROLL) + AGG_UNROLL - 1));
+#endif
+        st.flush(a, dpre, keys, ftau, nsteps - ftau);
     }
     if (NV) cta_barrier();
 }
@@ -735,7 +767,8 @@ int svb_launch_aggregate(svb_context *ctx, const SgbmPlan &pl, char *ws, size_t 
     a.one = 1;
     a.uniq = pl.p.uniquenessRatio;
     a.invalid16 = pl.invalid16;
-    a.slack = B > 1 ? 16 : 0;
+    a.slack = 0;   // (hysteresis for starving bands: measured no better than 0 since the edges are L2-prefetched)
+    if (const char *e = getenv("SVB_SWEEP_SLACK")) a.slack = atoi(e);   // tuning hook
     const int pad = pl.Dp != pl.D;
     const int NR = pl.E / 2;
     // pass 1: left, up-left, up, up-right
