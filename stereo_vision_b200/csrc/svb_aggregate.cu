@@ -177,6 +177,52 @@ __device__ __forceinline__ void finish_dir(uint32_t (&L)[NR], uint32_t (&s)[NR],
     }
 }
 
+template <int G>
+__device__ __forceinline__ uint32_t group_max_u32(uint32_t v)
+{
+#ifdef EXP_NOREDUX
+    return v;
+#endif
+    if (G == 32) return __reduce_max_sync(0xffffffffu, v);
+#pragma unroll
+    for (int o = G >> 1; o; o >>= 1) v = max(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+
+// finish_dir for two directions at once.  The two per-lane minima are folded side by side in one register
+// (3 ALU instructions instead of 2 x 3), complemented (0xFFFF - m = -m - 1 per half, no borrow) and reduced with
+// REDUX.MAX, whose result is then one add and one PRMT away from the packed -minL the normalisation needs
+// (instead of move, negate, mask, multiply): 6 ALU-pipe instructions fewer per pixel and a shorter dependent chain.
+template <int NR, int G, bool SAFE, bool PAD>
+__device__ __forceinline__ void finish_pair(uint32_t (&LA)[NR], uint32_t (&LB)[NR], uint32_t (&s)[NR], uint32_t P2d,
+                                            uint32_t one, const uint32_t (&keep)[NR])
+{
+    uint32_t mA = LA[0], mB = LB[0];
+#pragma unroll
+    for (int k = 1; k + 1 < NR; k += 2) { mA = __vimin3_s16x2(mA, LA[k], LA[k + 1]); mB = __vimin3_s16x2(mB, LB[k], LB[k + 1]); }
+    if ((NR & 1) == 0) { mA = __vmins2(mA, LA[NR - 1]); mB = __vmins2(mB, LB[NR - 1]); }
+    const uint32_t z = __vminu2(__byte_perm(mA, mB, 0x5410), __byte_perm(mA, mB, 0x7632));   // (min A, min B) of this lane
+    const uint32_t zc = z * (0u - one) + 0xFFFFFFFFu;                  // ~z on the FMA pipe
+    const uint32_t rB = group_max_u32<G>(zc);                          // high half: 0xFFFF - min_d L_B
+    const uint32_t rA = group_max_u32<G>(zc * (one << 16));            // high half: 0xFFFF - min_d L_A
+    const uint32_t negA = __byte_perm(rA * one + 0x10000u, 0u, 0x3232);   // (-minL) mod 2^16 in both halves (IMAD + PRMT)
+    const uint32_t negB = __byte_perm(rB * one + 0x10000u, 0u, 0x3232);
+#pragma unroll
+    for (int k = 0; k < NR; k++) {
+        if (SAFE) s[k] += LA[k] + LB[k];
+        else s[k] = __viaddmin_u16x2(__viaddmin_u16x2(s[k], LA[k], 0x7FFF7FFFu), LB[k], 0x7FFF7FFFu);
+        LA[k] = __viaddmin_s16x2(LA[k], negA, P2d);
+        LB[k] = __viaddmin_s16x2(LB[k], negB, P2d);
+    }
+    if (PAD) {
+#pragma unroll
+        for (int k = 0; k < NR; k++) {
+            LA[k] = (LA[k] & keep[k]) | (P2d & ~keep[k]);
+            LB[k] = (LB[k] & keep[k]) | (P2d & ~keep[k]);
+        }
+    }
+}
+
 template <int NR>
 __device__ __forceinline__ void ld_regs_shared(const int16_t *p, uint32_t (&r)[NR])
 {
@@ -286,6 +332,8 @@ struct SweepLane {
     static constexpr int E = 2 * NR;
     static constexpr int DP = G * E;                // padded disparities of this instantiation (== a.Dp)
     static constexpr int XDIR = PASS2 ? -1 : 1;     // pass 2 walks every row right to left (and the rows bottom-up)
+    // pass 2: selection one pixel-time behind the path updates (not for the single-path kernel: nothing to overlap with)
+    static constexpr bool SELPIPE = AGG_SELPIPE && NV > 0;
     // loop-invariant
     int W1, VS, lag, lane, y, xbase;                // x = xbase + XDIR*u
     bool rowActive, isRow0;
@@ -331,27 +379,30 @@ struct SweepLane {
         const int u = t - lag;
         const bool act = rowActive && (unsigned)u < (unsigned)W1;
         uint32_t c[NR], s[NR], L[NR];
-#if AGG_SELPIPE
-        if (PASS2)   // selection of pixel-time t-1 (slot PH-1 of this half, or the last slot of the other half)
+        if (PASS2 && SELPIPE)   // selection of pixel-time t-1 (slot PH-1 of this half, or the last slot of the other half)
             select<(PH + AGG_UNROLL - 1) % AGG_UNROLL>(PH ? parkw + (PH - 1) : park + (((parkw - park) ^ AGG_UNROLL) + AGG_UNROLL - 1));
-#endif
 #pragma unroll
         for (int k = 0; k < NR; k++) { c[k] = cbuf[PB][k]; s[k] = (PASS2 && !SAFE) ? sbuf[PH % PFS][k] : 0u; }
         prefetch_c<PB, PH + PFD>();
         if (!SAFE) prefetch_s<PH % PFS, PH + PFS>();
         // ---- horizontal path (registers) ----
+        uint32_t Lh[NR];
         {
-            const uint32_t hm = u > 0 ? 0xFFFFFFFFu : 0u;
+            if (PH % AGG_LAG == 0 || !NV) {   // the row starts (u == 0) at pixel-time lag = AGG_LAG * g only
+                const uint32_t hm = u > 0 ? 0xFFFFFFFFu : 0u;
 #pragma unroll
-            for (int k = 0; k < NR; k++) h[k] &= hm;
+                for (int k = 0; k < NR; k++) h[k] &= hm;
+            }
             uint32_t wprev = __shfl_up_sync(0xffffffffu, h[NR - 1], 1, G);
             uint32_t wnext = __shfl_down_sync(0xffffffffu, h[0], 1, G);
             if (lane == 0) wprev = P2d;
             if (lane == G - 1) wnext = P2d;
-            dir_update<NR>(h, wprev, wnext, c, P1d, a.one, L);
-            finish_dir<NR, G, SAFE, PAD>(L, s, P2d, keep);
+            dir_update<NR>(h, wprev, wnext, c, P1d, a.one, Lh);
+            if (!NV) {
+                finish_dir<NR, G, SAFE, PAD>(Lh, s, P2d, keep);
 #pragma unroll
-            for (int k = 0; k < NR; k++) h[k] = L[k];
+                for (int k = 0; k < NR; k++) h[k] = Lh[k];
+            }
         }
         // ---- vertical / diagonal paths: predecessors (u-1, u, u+1) of the previous row ----
         if (NV) {
@@ -361,6 +412,7 @@ struct SweepLane {
 #else
             const bool epred = act && edgeRow;
 #endif
+            uint32_t Lv[3][NR];
 #pragma unroll
             for (int j = 0; j < 3; j++) {
                 if (NV == 1 && j != 1) continue;   // MODE_HH4: the vertical predecessor only
@@ -372,10 +424,23 @@ struct SweepLane {
                 ld_regs_shared<NR>(src, p);
                 const uint32_t wprev = *reinterpret_cast<const uint32_t *>(src - 2);
                 const uint32_t wnext = *reinterpret_cast<const uint32_t *>(src + E);
-                dir_update<NR>(p, wprev, wnext, c, P1d, a.one, L);
-                finish_dir<NR, G, SAFE, PAD>(L, s, P2d, keep);
-                st_regs<NR>(wbase + ((PH % AGG_SLOTS) * 3 + j) * VS, L);
-                st_regs_cg_pred<NR>(eptr + (PH * 3 + j) * DP, L, epred);
+                dir_update<NR>(p, wprev, wnext, c, P1d, a.one, Lv[j]);
+                // the directions are finished in pairs: (horizontal, up-left) and (up, up-right); MODE_HH4: (horizontal, up)
+                if (j == (NV == 1 ? 1 : 0)) {
+                    finish_pair<NR, G, SAFE, PAD>(Lh, Lv[j], s, P2d, a.one, keep);
+#pragma unroll
+                    for (int k = 0; k < NR; k++) h[k] = Lh[k];
+                }
+                if (NV == 3 && j == 2) finish_pair<NR, G, SAFE, PAD>(Lv[1], Lv[2], s, P2d, a.one, keep);
+                if (NV == 1 || j != 1) {
+                    constexpr int J0 = 0;
+#pragma unroll
+                    for (int jj = (NV == 3 && j == 2) ? 1 : j; jj <= j; jj++) {
+                        st_regs<NR>(wbase + ((PH % AGG_SLOTS) * 3 + jj) * VS, Lv[jj]);
+                        st_regs_cg_pred<NR>(eptr + (PH * 3 + jj) * DP, Lv[jj], epred);
+                    }
+                    (void)J0;
+                }
             }
         }
         if (!PASS2) {
@@ -395,13 +460,9 @@ struct SweepLane {
                 if (PAD) s[k] |= 0x7FFF7FFFu & ~keep[k];
                 s[k] = __vminu2(s[k], 0x7FFF7FFFu);
             }
-#if AGG_SELPIPE
-            // the selection of this pixel runs one pixel-time later (select<>), interleaved with the next pixel's paths
+            // with SELPIPE the selection of this pixel runs one pixel-time later, interleaved with the next pixel's paths
             st_regs<NR>(scratch + (PH & 1) * DP + lane * E, s);
-#else
-            st_regs<NR>(scratch + (PH & 1) * DP + lane * E, s);
-            select<PH>(parkw + PH);
-#endif
+            if (!SELPIPE) select<PH>(parkw + PH);
         }
     }
 
@@ -656,15 +717,13 @@ __global__ void __launch_bounds__(NGRP *G + (NV ? 32 : 0)) k_sweep(const __grid_
 #undef SVB_STEP
         st.advance();
         if (PASS2 && ((t0 / AGG_UNROLL) & 1)) {   // every second iteration the parked pixels get their scalar tail
-            const int upto = t0 + AGG_UNROLL - AGG_SELPIPE;   // pixel-times < upto are parked
+            const int upto = t0 + AGG_UNROLL - (Lane::SELPIPE ? 1 : 0);   // pixel-times < upto are parked
             st.flush(a, dpre, keys, ftau, upto - ftau);
             ftau = upto;
         }
     }
     if (PASS2) {
-#if AGG_SELPIPE
-        st.template select<AGG_UNROLL - 1>(st.park + (((st.parkw - st.park) ^ AGG_UNROLL) + AGG_UNROLL - 1));
-#endif
+        if (Lane::SELPIPE) st.template select<AGG_UNROLL - 1>(st.park + (((st.parkw - st.park) ^ AGG_UNROLL) + AGG_UNROLL - 1));
         st.flush(a, dpre, keys, ftau, nsteps - ftau);
     }
     if (NV) cta_barrier();
