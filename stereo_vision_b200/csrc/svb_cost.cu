@@ -275,7 +275,6 @@ __device__ __forceinline__ void cost_phase2(const CostP2 &q, int kofs, int16_t *
         acc[k][2] += hs[2] - old[k].z; acc[k][3] += hs[3] - old[k].w;     // acc >= old per half: no borrow
         if (EMIT) {
             uint32_t o[4] = {acc[k][0], acc[k][1], acc[k][2], acc[k][3]};
-            if (!q.live) o[0] = o[1] = o[2] = o[3] = 0;      // MODE_HH4: rows whose window leaves the image stay 0
             if (q.padded) {                                     // padded disparities carry CPAD (CTA-uniform branch)
 #pragma unroll
                 for (int j = 0; j < 4; j++) {
@@ -454,8 +453,22 @@ struct CostConsumer {
             q.ringcell = ringcell0 + (uint32_t)slot * slot_bytes;
             q.live = y < zrow;
             int16_t *cout = reinterpret_cast<int16_t *>(reinterpret_cast<char *>(cout0) + (ptrdiff_t)y * (ptrdiff_t)crow);
-            if (r >= t.ya + R) cost_phase2_row<BS, true>(q, cout, acc);
-            else cost_phase2_row<BS, false>(q, cout, acc);
+            if (r < t.ya + R) cost_phase2_row<BS, false>(q, cout, acc);
+            else if (q.live) cost_phase2_row<BS, true>(q, cout, acc);
+            else {   // MODE_HH4: rows whose window leaves the image stay 0 (CTA-uniform; every later row of the image is
+                     // dead too, so the running sums are not needed any more)
+#pragma unroll
+                for (int k = 0; k < COST_CPB_MAX; k++) {
+                    uint32_t o[4] = {0u, 0u, 0u, 0u};
+                    if (q.padded) {
+#pragma unroll
+                        for (int j = 0; j < 4; j++)
+                            o[j] = q.cpad & ~(((q.lane * 8 + 2 * j < q.D) ? 0x0000FFFFu : 0u) |
+                                              ((q.lane * 8 + 2 * j + 1 < q.D) ? 0xFFFF0000u : 0u));
+                    }
+                    stg128_pred(reinterpret_cast<char *>(cout) + (size_t)k * q.Dp2, o[0], o[1], o[2], o[3], q.cmask >> k & 1);
+                }
+            }
         }
         slot = slot + 1 == BS ? 0 : slot + 1;
     }
