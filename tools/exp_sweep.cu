@@ -6,7 +6,10 @@ void svb_set_error(const char *, ...) {}
 int main(int argc, char **argv)
 {
     const int H = argc > 2 ? atoi(argv[2]) : 15, W1 = 1664, Dp = 256, B = argc > 1 ? atoi(argv[1]) : 148, W = 1920;
-    const int NB = (H + 14) / 15;
+#ifndef HNG
+#define HNG 15
+#endif
+    const int NB = (H + HNG - 1) / HNG;
     const size_t vol = (size_t)H * W1 * Dp * 2, edge = (size_t)NB * W1 * 3 * Dp * 2;
     const size_t stride = ((2 * vol + edge + 4096 + (size_t)H * W * 6) + 255) / 256 * 256 + 256;
     char *ws; cudaMalloc(&ws, stride * B + (1 << 20));
@@ -33,15 +36,15 @@ int main(int argc, char **argv)
             for (int b = 0; b < B; b++) cudaMemset(ws + b * stride + 2 * vol + edge, 0, 4096);
             a.ticket = tick; a.flip = pass; a.prog = (unsigned *)(ws + 2 * vol + edge) + pass * 512;
             cudaEventRecord(e0);
-            if (pass == 0) launch_sweep_t<4, 32, 15, 3, false, true, false>(a, B * NB, 0);
-            else launch_sweep_t<4, 32, 15, 3, true, true, false>(a, B * NB, 0);
+            if (pass == 0) launch_sweep_t<4, 32, HNG, 3, false, true, false>(a, B * NB, 0);
+            else launch_sweep_t<4, 32, HNG, 3, true, true, false>(a, B * NB, 0);
             cudaEventRecord(e1); cudaEventSynchronize(e1);
             float ms; cudaEventElapsedTime(&ms, e0, e1); if (ms < best) best = ms;
         }
         unsigned long long sp[4]; cudaMemcpyFromSymbol(sp, g_spin, sizeof sp); unsigned long long z[4] = {0,0,0,0}; cudaMemcpyToSymbol(g_spin, z, sizeof z);
         printf("   starved steps %.2f%% of consumer steps, spin cycles per consumer step %.1f\n", 100.0 * sp[0] / (sp[2] + 1), (double)sp[1] / (sp[2] + 1));
         cudaError_t e = cudaGetLastError();
-        const double steps = 1696.0 * B * NB / 148.0;
+        const double steps = 1696.0 * B * NB / 148.0 / (HNG <= 8 ? 2 : 1);
         printf("pass%d B=%d: %.3f ms  -> %.0f cycles/step @1.965GHz  (%s)\n", pass + 1, B, best, best * 1e-3 / steps * 1.965e9, cudaGetErrorString(e));
     }
     return 0;
