@@ -274,8 +274,8 @@ def run_ours(args):
         "gpix_disp_per_s": fps * W * H * D / 1e9,
         "config": {"workload": WORKLOAD, "frames_per_step_per_gpu": B, "parallelism": f"frame-pair sharding x{world}, no collective",
                    "l2": "per-step working set (C+S volumes, %.1f GB/GPU) >> 126 MB L2; no explicit flush" % (2 * 2.0 * W1 * H * Dp * B / 1e9)},
-        "e2e": {"value": fps_e2e, "unit": "frames/s", "h2d_bytes_per_step": int(2 * B * H * W),
-                "d2h_bytes_per_step": int(B * H * W * 2 + B * NBOX * 4), "gpix_disp_per_s": fps_e2e * W * H * D / 1e9},
+        "e2e": {"value": fps_e2e, "unit": "frames/s", "h2d_bytes_per_step": int(2 * B * H * W) * world,                 # all ranks
+                "d2h_bytes_per_step": int(B * H * W * 2 + B * NBOX * 4) * world, "gpix_disp_per_s": fps_e2e * W * H * D / 1e9},
         "gpu_launches": 11 * args.steps,   # planes, cost, sweep x2, lrcheck, median3, ccl x4, box_median
         "clocks": clocks,
         "stage_ms_per_step": stage_ms,
