@@ -123,26 +123,39 @@ __device__ __forceinline__ void uf_union(int *L, int a, int b)
     }
 }
 
-// Phase 1: per-row runs.  label = index of the first pixel of the horizontal run (no atomics needed).
+// Phase 1: per-row runs.  label = index of the first pixel of the horizontal run inside the CTA's 256-pixel segment, or
+// — for the run that continues from the previous segment — of that segment's last pixel, whose own label points
+// further left: every label points left inside the same run, which is all the union-find of the later phases needs
+// (chains are at most W/256 hops long).  One ballot per warp + a look-back over the CTA's 8 warps instead of a
+// per-pixel backward walk.
 __global__ void __launch_bounds__(256) k_ccl_init(const int16_t *__restrict__ img, int *__restrict__ L, int H, int W,
                                                   size_t pitch, size_t stride, int newVal, int maxDiff, size_t lstride)
 {
-    // one warp per row segment would be faster; rows are short (<= few K px) so a simple backward walk capped
-    // at 32 px keeps chains short and the merge phase links the rest.
+    __shared__ int s_start[8];   // per warp: x of the last run start in its 32 pixels, -1 if all 32 continue a run
     const int x = blockIdx.x * blockDim.x + threadIdx.x;
     const int y = blockIdx.y, b = blockIdx.z;
-    if (x >= W) return;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int16_t *row = img + (size_t)b * stride + (size_t)y * pitch;
     int *Lr = L + (size_t)b * lstride + (size_t)y * W;
-    int v = row[x];
-    if (v == newVal) { Lr[x] = -1; return; }
-    int xs = x;
-#pragma unroll 1
-    for (int k = 0; k < 32 && xs > 0; k++) {
-        int u = row[xs - 1];
-        if (u == newVal || abs(u - v) > maxDiff) break;
-        v = u;
-        xs--;
+    const bool in = x < W;
+    const int v = in ? row[x] : newVal;
+    int u = __shfl_up_sync(0xffffffffu, v, 1);
+    if (lane == 0) u = (in && x > 0) ? row[x - 1] : newVal;
+    const bool valid = in && v != newVal;
+    const bool linked = valid && u != newVal && abs(u - v) <= maxDiff;     // same run as pixel x-1
+    const unsigned brk = __ballot_sync(0xffffffffu, !linked);              // bit i: a run starts (or no run is) at lane i
+    if (lane == 0) s_start[wid] = brk ? x + 31 - __clz(brk) : -1;
+    __syncthreads();
+    if (!in) return;
+    if (!valid) { Lr[x] = -1; return; }
+    const unsigned below = brk & (0xffffffffu >> (31 - lane));             // run starts at or below this lane
+    int xs;
+    if (below) xs = x - lane + (31 - __clz(below));
+    else {   // the run continues from the pixels on the left: last start among the CTA's earlier warps, else the
+             // previous CTA's last pixel
+        xs = (int)(blockIdx.x * blockDim.x) - 1;
+        for (int w = wid - 1; w >= 0; w--)
+            if (s_start[w] >= 0) { xs = s_start[w]; break; }
     }
     Lr[x] = y * W + xs;
 }
