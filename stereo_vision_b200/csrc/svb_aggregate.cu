@@ -78,6 +78,7 @@ struct AggArgs {
     int flip;              // 0: rows top-down, x ascending; 1: both reversed
     uint32_t P1d, P2d;     // duplicated halves
     uint32_t one;          // == 1 (an opaque multiplier: x * one + y stays an IMAD on the FMA pipe)
+    uint32_t k16;          // == 65536, likewise (x * k16 + y instead of a PRMT / shift on the ALU pipe)
     int uniq, invalid16;
     int slack;             // extra producer lead a starving band waits for (0 when one frame is in flight)
 };
@@ -380,7 +381,7 @@ struct SweepLane {
         const bool act = rowActive && (unsigned)u < (unsigned)W1;
         uint32_t c[NR], s[NR], L[NR];
         if (PASS2 && SELPIPE)   // selection of pixel-time t-1 (slot PH-1 of this half, or the last slot of the other half)
-            select<(PH + AGG_UNROLL - 1) % AGG_UNROLL>(PH ? parkw + (PH - 1) : park + (((parkw - park) ^ AGG_UNROLL) + AGG_UNROLL - 1));
+            select<(PH + AGG_UNROLL - 1) % AGG_UNROLL>(PH ? parkw + (PH - 1) : park + (((parkw - park) ^ AGG_UNROLL) + AGG_UNROLL - 1), a.k16);
 #pragma unroll
         for (int k = 0; k < NR; k++) { c[k] = cbuf[PB][k]; s[k] = (PASS2 && !SAFE) ? sbuf[PH % PFS][k] : 0u; }
         prefetch_c<PB, PH + PFD>();
@@ -462,13 +463,13 @@ struct SweepLane {
             }
             // with SELPIPE the selection of this pixel runs one pixel-time later, interleaved with the next pixel's paths
             st_regs<NR>(scratch + (PH & 1) * DP + lane * E, s);
-            if (!SELPIPE) select<PH>(parkw + PH);
+            if (!SELPIPE) select<PH>(parkw + PH, a.k16);
         }
     }
 
     // pass 2: winner / second best / subpixel taps of the pixel whose clamped S sits in scratch half PHP & 1
     template <int PHP>
-    __device__ __forceinline__ void select(uint4 *dst)
+    __device__ __forceinline__ void select(uint4 *dst, uint32_t k16)
     {
         const int16_t *sc = scratch + (PHP & 1) * DP;
         __syncwarp();
@@ -479,7 +480,7 @@ struct SweepLane {
         uint32_t lk = 0xFFFFFFFFu;
 #pragma unroll
         for (int k = 0; k < NR; k++) {
-            lk = min(lk, __byte_perm(s[k], d0 + 2 * k, 0x1054));       // (S_lo << 16) | d
+            lk = min(lk, s[k] * k16 + (d0 + 2 * k));                   // (S_lo << 16) | d, as an IMAD (FMA pipe)
             lk = min(lk, __byte_perm(s[k], d0 + 2 * k + 1, 0x3254));   // (S_hi << 16) | d
         }
         const uint32_t best = group_min_u32<G>(lk);
@@ -723,7 +724,7 @@ __global__ void __launch_bounds__(NGRP *G + (NV ? 32 : 0)) k_sweep(const __grid_
         }
     }
     if (PASS2) {
-        if (Lane::SELPIPE) st.template select<AGG_UNROLL - 1>(st.park + (((st.parkw - st.park) ^ AGG_UNROLL) + AGG_UNROLL - 1));
+        if (Lane::SELPIPE) st.template select<AGG_UNROLL - 1>(st.park + (((st.parkw - st.park) ^ AGG_UNROLL) + AGG_UNROLL - 1), a.k16);
         st.flush(a, dpre, keys, ftau, nsteps - ftau);
     }
     if (NV) cta_barrier();
@@ -824,6 +825,7 @@ int svb_launch_aggregate(svb_context *ctx, const SgbmPlan &pl, char *ws, size_t 
     a.P1d = (uint32_t)pl.p.P1 * 0x10001u;
     a.P2d = (uint32_t)pl.p.P2 * 0x10001u;
     a.one = 1;
+    a.k16 = 65536;
     a.uniq = pl.p.uniquenessRatio;
     a.invalid16 = pl.invalid16;
     a.slack = 0;   // (hysteresis for starving bands: measured no better than 0 since the edges are L2-prefetched)
