@@ -160,7 +160,7 @@ __global__ void __launch_bounds__(BOX_THREADS) k_box_median(const int16_t *__res
 {
     __shared__ unsigned hist[BOX_WARPS][256];
     __shared__ unsigned tot[256];
-    __shared__ unsigned s_prefix, s_rank, s_n;
+    __shared__ unsigned s_prefix, s_rank, s_n, s_eq;
     const int b = blockIdx.x;
     const int tid = threadIdx.x, wid = tid >> 5;
     const int16_t *disp = disp16 + (size_t)(box_image ? box_image[b] : 0) * stride;
@@ -172,62 +172,76 @@ __global__ void __launch_bounds__(BOX_THREADS) k_box_median(const int16_t *__res
         g.x1 = x1; g.y1 = y1; g.bw = max(x2 - x1, 0); g.bh = max(y2 - y1, 0);
     }
     const int area = g.bw * g.bh;
-    // count valid
-    if (tid == 0) s_n = 0;
-    __syncthreads();
-    unsigned cnt = 0;
-    for (int i = tid; i < area; i += BOX_THREADS) {
-        unsigned k;
-        cnt += box_key(disp, W, Q, invalid16, g, i, k) ? 1u : 0u;
-    }
-    cnt = __reduce_add_sync(0xffffffffu, cnt);
-    if ((tid & 31) == 0 && cnt) atomicAdd(&s_n, cnt);
-    __syncthreads();
-    const unsigned n = s_n;
-    if (n == 0) {
-        if (tid == 0) out[b] = __int_as_float(0x7fc00000);
-        return;
-    }
-    float res[2];
-    const unsigned ranks[2] = {(n - 1) / 2, n / 2};
-    for (int rsel = 0; rsel < 2; rsel++) {
-        if (rsel == 1 && ranks[1] == ranks[0]) { res[1] = res[0]; break; }
-        unsigned prefix = 0, mask = 0, rank = ranks[rsel];
-        for (int shift = 24; shift >= 0; shift -= 8) {
-            for (int i = tid; i < BOX_WARPS * 256; i += BOX_THREADS) (&hist[0][0])[i] = 0;
-            __syncthreads();
-            for (int i = tid; i < area; i += BOX_THREADS) {
-                unsigned k;
-                if (box_key(disp, W, Q, invalid16, g, i, k) && (k & mask) == prefix)
-                    atomicAdd(&hist[wid][(k >> shift) & 255u], 1u);
-            }
-            __syncthreads();
-            if (tid < 256) {
-                unsigned s = 0;
-#pragma unroll
-                for (int w = 0; w < BOX_WARPS; w++) s += hist[w][tid];
-                tot[tid] = s;
-            }
-            __syncthreads();
-            if (tid == 0) {
-                unsigned cum = 0;
-                int bin = 0;
-                for (; bin < 256; bin++) {
-                    if (cum + tot[bin] > rank) break;
-                    cum += tot[bin];
-                }
-                s_prefix = prefix | ((unsigned)bin << shift);
-                s_rank = rank - cum;
-            }
-            __syncthreads();
-            prefix = s_prefix;
-            rank = s_rank;
-            mask |= 255u << shift;
-            __syncthreads();
+    // Radix select, 8 bits per pass.  The first pass (top byte, no prefix) also counts the valid pixels; the lower
+    // median comes out after four passes together with the number of keys below / equal to it, so the upper median
+    // (even counts) is either the same value or the smallest key above it: one more pass instead of four.
+    unsigned prefix = 0, mask = 0, rank = 0, n = 0, below = 0, eq = 0;
+    for (int shift = 24; shift >= 0; shift -= 8) {
+        for (int i = tid; i < BOX_WARPS * 256; i += BOX_THREADS) (&hist[0][0])[i] = 0;
+        __syncthreads();
+        for (int i = tid; i < area; i += BOX_THREADS) {
+            unsigned k;
+            if (box_key(disp, W, Q, invalid16, g, i, k) && (k & mask) == prefix)
+                atomicAdd(&hist[wid][(k >> shift) & 255u], 1u);
         }
-        res[rsel] = fkey_inv(prefix);
+        __syncthreads();
+        if (tid < 256) {
+            unsigned t = 0;
+#pragma unroll
+            for (int w = 0; w < BOX_WARPS; w++) t += hist[w][tid];
+            tot[tid] = t;
+        }
+        __syncthreads();
+        if (tid == 0) {
+            unsigned r = rank;
+            if (shift == 24) {   // total count -> rank of the lower median
+                unsigned c = 0;
+                for (int bin = 0; bin < 256; bin++) c += tot[bin];
+                s_n = c;
+                r = c ? (c - 1) / 2 : 0;
+            }
+            unsigned cum = 0;
+            int bin = 0;
+            for (; bin < 255; bin++) {
+                if (cum + tot[bin] > r) break;
+                cum += tot[bin];
+            }
+            s_prefix = prefix | ((unsigned)bin << shift);
+            s_rank = r - cum;
+            s_eq = tot[bin];
+        }
+        __syncthreads();
+        if (shift == 24) {
+            n = s_n;
+            if (n == 0) {
+                if (tid == 0) out[b] = __int_as_float(0x7fc00000);
+                return;
+            }
+            rank = (n - 1) / 2;
+        }
+        below += rank - s_rank;      // keys smaller than every key that still matches the prefix
+        prefix = s_prefix;
+        rank = s_rank;
+        eq = s_eq;
+        mask |= 255u << shift;
+        __syncthreads();
     }
-    if (tid == 0) out[b] = (ranks[0] == ranks[1]) ? res[0] : __fmul_rn(__fadd_rn(res[0], res[1]), 0.5f);
+    const float lo = fkey_inv(prefix);
+    float hi = lo;
+    if ((n & 1u) == 0 && n / 2 >= below + eq) {   // the upper median is the next larger key
+        if (tid == 0) s_prefix = 0xFFFFFFFFu;
+        __syncthreads();
+        unsigned m = 0xFFFFFFFFu;
+        for (int i = tid; i < area; i += BOX_THREADS) {
+            unsigned k;
+            if (box_key(disp, W, Q, invalid16, g, i, k) && k > prefix) m = min(m, k);
+        }
+        m = __reduce_min_sync(0xffffffffu, m);
+        if ((tid & 31) == 0) atomicMin(&s_prefix, m);
+        __syncthreads();
+        hi = fkey_inv(s_prefix);
+    }
+    if (tid == 0) out[b] = (n & 1u) ? lo : __fmul_rn(__fadd_rn(lo, hi), 0.5f);
 }
 
 extern "C" int svb_box_median_depth(svb_context *ctx, const int16_t *disp16, int H, int W, size_t stride_elems,
