@@ -178,7 +178,7 @@ __device__ __forceinline__ int cv_round_x86(float v)
 }
 __device__ __forceinline__ int sat16(int v) { return max(-32768, min(32767, v)); }
 
-template <int C>
+template <int C, bool WORDS = false>
 __device__ __forceinline__ void remap_fixed(const uint8_t *__restrict__ src, int sH, int sW, size_t spitch, int ix, int iy,
                                             int fx, int fy, uint8_t *o)
 {
@@ -188,6 +188,29 @@ __device__ __forceinline__ void remap_fixed(const uint8_t *__restrict__ src, int
     const uint8_t *r0 = src + (size_t)(y0 ? iy : 0) * spitch;
     const uint8_t *r1 = src + (size_t)(y1 ? iy + 1 : 0) * spitch;
     const int xa = (x0 ? ix : 0) * C, xb = (x1 ? ix + 1 : 0) * C;
+    if (WORDS) {
+        // interior pixel: the 2*C bytes of both taps of a row are consecutive -> aligned 32-bit loads + funnel shifts
+        // instead of 2*C byte loads per row.  The caller guarantees 4-byte aligned rows; the last words of a row are
+        // left to the byte path.
+        constexpr int NWORD = C == 1 ? 2 : 3;
+        const int a0 = xa & ~3, sh = (xa & 3) * 8;
+        if (y0 && y1 && x0 && x1 && a0 + 4 * NWORD <= sW * C) {
+            const uint32_t *p0 = reinterpret_cast<const uint32_t *>(r0 + a0);
+            const uint32_t *p1 = reinterpret_cast<const uint32_t *>(r1 + a0);
+            const uint32_t a = __ldg(p0), b = __ldg(p0 + 1), c2 = NWORD > 2 ? __ldg(p0 + 2) : 0u;
+            const uint32_t d = __ldg(p1), e = __ldg(p1 + 1), f2 = NWORD > 2 ? __ldg(p1 + 2) : 0u;
+            const uint32_t lo0 = __funnelshift_r(a, b, sh), hi0 = __funnelshift_r(b, c2, sh);   // bytes 0..3 / 4..7 from xa
+            const uint32_t lo1 = __funnelshift_r(d, e, sh), hi1 = __funnelshift_r(e, f2, sh);
+            const unsigned long long q0 = ((unsigned long long)hi0 << 32) | lo0, q1 = ((unsigned long long)hi1 << 32) | lo1;
+#pragma unroll
+            for (int c = 0; c < C; c++) {
+                const int t00 = (int)((q0 >> (8 * c)) & 255u), t01 = (int)((q0 >> (8 * (c + C))) & 255u);
+                const int t10 = (int)((q1 >> (8 * c)) & 255u), t11 = (int)((q1 >> (8 * (c + C))) & 255u);
+                o[c] = (uint8_t)((w00 * t00 + w01 * t01 + w10 * t10 + w11 * t11 + 16384) >> 15);
+            }
+            return;
+        }
+    }
 #pragma unroll
     for (int c = 0; c < C; c++) {
         int t00 = (y0 && x0) ? (int)__ldg(r0 + xa + c) : 0;
@@ -198,12 +221,12 @@ __device__ __forceinline__ void remap_fixed(const uint8_t *__restrict__ src, int
     }
 }
 
-template <int C>
+template <int C, bool WORDS = false>
 __device__ __forceinline__ void remap_px(const uint8_t *__restrict__ src, int sH, int sW, size_t spitch, float mx,
                                          float my, uint8_t *o)
 {
     const int sx = cv_round_x86(mx * 32.0f), sy = cv_round_x86(my * 32.0f);
-    remap_fixed<C>(src, sH, sW, spitch, sat16(sx >> 5), sat16(sy >> 5), sx & 31, sy & 31, o);
+    remap_fixed<C, WORDS>(src, sH, sW, spitch, sat16(sx >> 5), sat16(sy >> 5), sx & 31, sy & 31, o);
 }
 
 // one thread = 4 consecutive destination pixels (vector map loads, word stores when aligned)
@@ -221,13 +244,21 @@ __global__ void __launch_bounds__(256) k_remap_u8(const uint8_t *__restrict__ sr
     uint8_t *drow = dst + (size_t)b * dstride + (size_t)y * dpitch;
     const size_t mi = (size_t)y * dW + x4;
     if (vec_ok && x4 + 4 <= dW) {
-        const float4 mx = __ldcs(reinterpret_cast<const float4 *>(mapx + mi));
-        const float4 my = __ldcs(reinterpret_cast<const float4 *>(mapy + mi));
+        // default caching: the maps are shared by the B frames of a batch and stay L2-resident between them
+        const float4 mx = __ldg(reinterpret_cast<const float4 *>(mapx + mi));
+        const float4 my = __ldg(reinterpret_cast<const float4 *>(mapy + mi));
         __align__(4) uint8_t o[4 * C];
-        remap_px<C>(src, sH, sW, spitch, mx.x, my.x, o + 0 * C);
-        remap_px<C>(src, sH, sW, spitch, mx.y, my.y, o + 1 * C);
-        remap_px<C>(src, sH, sW, spitch, mx.z, my.z, o + 2 * C);
-        remap_px<C>(src, sH, sW, spitch, mx.w, my.w, o + 3 * C);
+        if (vec_ok & 2) {   // source rows 4-byte aligned: word gathers
+            remap_px<C, true>(src, sH, sW, spitch, mx.x, my.x, o + 0 * C);
+            remap_px<C, true>(src, sH, sW, spitch, mx.y, my.y, o + 1 * C);
+            remap_px<C, true>(src, sH, sW, spitch, mx.z, my.z, o + 2 * C);
+            remap_px<C, true>(src, sH, sW, spitch, mx.w, my.w, o + 3 * C);
+        } else {
+            remap_px<C>(src, sH, sW, spitch, mx.x, my.x, o + 0 * C);
+            remap_px<C>(src, sH, sW, spitch, mx.y, my.y, o + 1 * C);
+            remap_px<C>(src, sH, sW, spitch, mx.z, my.z, o + 2 * C);
+            remap_px<C>(src, sH, sW, spitch, mx.w, my.w, o + 3 * C);
+        }
         uint32_t *dw = reinterpret_cast<uint32_t *>(drow + (size_t)x4 * C);
         const uint32_t *ow = reinterpret_cast<const uint32_t *>(o);
 #pragma unroll
@@ -250,8 +281,9 @@ extern "C" int svb_remap_u8(svb_context *ctx, const uint8_t *src, int sH, int sW
     SVB_REQUIRE(sH > 0 && sW > 0 && dH > 0 && dW > 0 && B > 0, SVB_ERR_INVALID, "remap: bad size");
     SVB_REQUIRE(sH < 32768 && sW < 32768, SVB_ERR_INVALID, "remap: source larger than SHRT_MAX (cv2 asserts too)");
     SVB_CUDA_CHECK(cudaSetDevice(ctx->device));
-    const int vec_ok = (dW % 4 == 0) && (((uintptr_t)mapx | (uintptr_t)mapy) % 16 == 0) && ((uintptr_t)dst % 4 == 0) &&
-                       (dpitch % 4 == 0) && (dstride % 4 == 0);
+    int vec_ok = (dW % 4 == 0) && (((uintptr_t)mapx | (uintptr_t)mapy) % 16 == 0) && ((uintptr_t)dst % 4 == 0) &&
+                 (dpitch % 4 == 0) && (dstride % 4 == 0);
+    if (vec_ok && (uintptr_t)src % 4 == 0 && spitch % 4 == 0 && sstride % 4 == 0) vec_ok |= 2;   // word gathers
     dim3 grid(((dW + 3) / 4 + 127) / 128, dH, B);
     if (C == 1)
         k_remap_u8<1><<<grid, 128, 0, (cudaStream_t)stream>>>(src, sH, sW, spitch, sstride, mapx, mapy, dst, dH, dW,
