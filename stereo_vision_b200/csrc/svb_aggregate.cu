@@ -33,10 +33,7 @@
 #ifndef AGG_SELPIPE
 #define AGG_SELPIPE 1      // pass 2: the selection of a pixel runs during the next pixel's path updates
 #endif
-#ifndef AGG_PPS
-#define AGG_PPS 2          // pixels every row advances per CTA barrier
-#endif
-#if AGG_PPS == 2
+#define AGG_PPS 2          // pixels every row advances per CTA barrier (one pixel per barrier: 9 % / 7 % slower)
 #define AGG_LAG 3          // row v trails row v-1 by AGG_LAG pixels (PPS + 1: the u+1 predecessor is one barrier old)
 #define AGG_SLOTS 6        // ring depth: a vector is read up to LAG+1 pixel-times after it was written, i.e. two
                            // barriers later, and its slot is rewritten SLOTS/PPS barriers later
@@ -44,18 +41,17 @@
 #define AGG_EPF 8          // cross-band prefetch distance: at pixel-time t pixels <= t+EPF may be issued; the slot of
                            // pixel t+EPF holds pixel t+EPF-ENS, which row 0 may still be reading during the previous
                            // barrier interval unless EPF <= ENS-PPS-2
+// Kernels with G == 32 lanes per row (Dp >= 256) use only AGG_SLOTS slots of that ring, phased like a row's own ring
+// (pixel pe in slot (pe + SLOTS - LAG) % SLOTS): row 0 then addresses its predecessors exactly like every other row
+// (no per-direction select; 3 % off pass 2, whose register allocation is at the limit).  The price is no fetch slack
+// (EPF = SLOTS - PPS - 2 = 2 while row 0 needs pixels <= t+PPS: every cp.async has to land within its own barrier
+// interval).  That holds for the long intervals of Dp >= 256 because the vectors were prefetched into L2 (AGG_L2PF);
+// with the short intervals of Dp = 128 it made pass 1 25 % slower, hence the compile-time switch.
+#define AGG_EDGE_LIKE_ROW(G) ((G) == 32)
 #define AGG_UNROLL 12      // pixel-times per loop iteration: a multiple of SLOTS, ENS, PPS and the prefetch depths
-#else
-#define AGG_LAG 2
-#define AGG_SLOTS 4        // ring depth (u-1, u, u+1 live + one being written)
-#define AGG_ENS 8
-#define AGG_EPF 5          // <= ENS-3
-#define AGG_UNROLL 8
-#endif
 #ifndef AGG_PUB
-#define AGG_PUB 8
+#define AGG_PUB 8          // publish cross-band progress every AGG_PUB pixels
 #endif
-//          // publish cross-band progress every AGG_PUB pixels
 #ifndef AGG_L2PF
 #define AGG_L2PF 32        // cross-band L2 prefetch distance (pixels ahead of the cp.async front), 0 = off
 #endif
@@ -419,7 +415,7 @@ struct SweepLane {
                 if (NV == 1 && j != 1) continue;   // MODE_HH4: the vertical predecessor only
                 const int offv = (((PH + AGG_SLOTS - 1 - AGG_LAG + j) % AGG_SLOTS) * 3 + j) * VS;   // written LAG+1-j pixel-times ago
                 const int offe = (((PH + AGG_ENS - 1 + j) % AGG_ENS) * 3 + j) * VS;               // pixel u-1+j, u == t
-                const int16_t *src = prevL + (isRow0 ? offe : offv);
+                const int16_t *src = prevL + ((!AGG_EDGE_LIKE_ROW(G) && isRow0) ? offe : offv);
                 if (j == 2 && u + 1 >= W1) src = zeroL;
                 uint32_t p[NR];
                 ld_regs_shared<NR>(src, p);
@@ -588,7 +584,8 @@ __global__ void __launch_bounds__(NGRP *G + (NV ? 32 : 0)) k_sweep(const __grid_
 #else
             const int16_t *src = edge_in + (size_t)pe * 3 * Dp;
 #endif
-            int16_t *dst = rowm1 + (size_t)((pe % AGG_ENS) * 3) * VS + AGG_PADE;
+            const int slot = AGG_EDGE_LIKE_ROW(G) ? (pe + AGG_SLOTS - AGG_LAG) % AGG_SLOTS : pe % AGG_ENS;
+            int16_t *dst = rowm1 + (size_t)(slot * 3) * VS + AGG_PADE;
 #ifndef EXP_NOFETCH
 #pragma unroll
             for (int i0 = 0; i0 < NCH; i0 += 32) {
@@ -638,7 +635,8 @@ __global__ void __launch_bounds__(NGRP *G + (NV ? 32 : 0)) k_sweep(const __grid_
                   if (lane == 0) atomicAdd(&g_spin[1], (unsigned long long)(clock64() - c0)); }
                 if (lane == 0) atomicAdd(&g_spin[2], 1ull);
 #endif
-                const int limit = min(min(t + 1 + AGG_EPF, W1), (int)known);
+                constexpr int EPF = AGG_EDGE_LIKE_ROW(G) ? AGG_SLOTS - AGG_PPS - 2 : AGG_EPF;
+                const int limit = min(min(t + 1 + EPF, W1), (int)known);
 #pragma unroll
                 for (int i = 0; i < 2 * AGG_PPS; i++)
                     if (fetched < limit) fetch(fetched++);
