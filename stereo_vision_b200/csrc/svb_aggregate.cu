@@ -732,7 +732,10 @@ __global__ void __launch_bounds__(NGRP *G + (NV ? 32 : 0)) k_sweep(const __grid_
 template <int NR, int G, int NGRP, int NV, bool PASS2, bool SAFE, bool PAD>
 static int launch_sweep_t(const AggArgs &a, int ngrid, cudaStream_t st)
 {
-    constexpr int PFD = NR == 4 ? 4 : 2;
+#ifndef AGG_PFD2
+#define AGG_PFD2 4
+#endif
+    constexpr int PFD = NR == 4 ? (PASS2 ? AGG_PFD2 : 4) : 2;   // C prefetch depth in pixels (pass 2 is short of registers)
     const size_t smem = SweepSmem<NGRP, NV, PASS2>::bytes(a.Dp, 2 * NR);
     auto kern = k_sweep<NR, G, NGRP, NV, PASS2, SAFE, PAD, PFD>;
     static size_t configured = 0;
