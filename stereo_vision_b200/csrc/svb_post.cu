@@ -190,20 +190,41 @@ __global__ void __launch_bounds__(256) k_ccl_merge(const int16_t *__restrict__ i
 
 __global__ void __launch_bounds__(256) k_ccl_count(int *__restrict__ L, int H, int W, size_t lstride)
 {
+    __shared__ int s_root[8], s_cnt[8];
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     const int b = blockIdx.z;
-    if (i >= H * W) return;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     int *Lb = L + (size_t)b * lstride;
     int *Sz = Lb + (size_t)H * W;
-    int l = Lb[i];
-    if (l < 0) return;
-    int r = uf_find(Lb, i);
-    Lb[i] = r;   // benign race: only ever shortens chains towards the same root
-    // warp-aggregated count: lanes that share a root elect one leader (large components would otherwise
-    // serialise ~W*H same-address atomics in L2)
-    const unsigned act = __activemask();
-    const unsigned same = __match_any_sync(act, r);
-    if ((int)(__ffs(same) - 1) == (int)(threadIdx.x & 31)) atomicAdd(&Sz[r], __popc(same));
+    int r = -1;
+    if (i < H * W && Lb[i] >= 0) {
+        r = uf_find(Lb, i);
+        Lb[i] = r;   // benign race: only ever shortens chains towards the same root
+    }
+    // Two-level aggregated count: lanes that share a root elect one leader (large components would otherwise
+    // serialise ~W*H same-address atomics in L2); the group of each warp's first labelled lane is then merged across
+    // the CTA's 8 warps, so that a component covering the whole CTA costs one atomic per 256 pixels, not eight.
+    const unsigned lab = __ballot_sync(0xffffffffu, r >= 0);
+    const unsigned same = __match_any_sync(0xffffffffu, r);
+    const int first = lab ? __ffs(lab) - 1 : 0;
+    const int r0 = __shfl_sync(0xffffffffu, r, first);
+    if (lane == 0) { s_root[wid] = lab ? r0 : -1; s_cnt[wid] = 0; }
+    __syncwarp();
+    if (r >= 0 && (int)(__ffs(same) - 1) == lane) {
+        if (r == r0) s_cnt[wid] = __popc(same);
+        else atomicAdd(&Sz[r], __popc(same));
+    }
+    __syncthreads();
+    if (threadIdx.x < 8 && s_root[threadIdx.x] >= 0) {
+        const int w = threadIdx.x, rw = s_root[w];
+        bool lead = true;
+        for (int k = 0; k < w; k++) lead = lead && s_root[k] != rw;
+        if (lead) {
+            int c = 0;
+            for (int k = w; k < 8; k++) c += (s_root[k] == rw) ? s_cnt[k] : 0;
+            atomicAdd(&Sz[rw], c);
+        }
+    }
 }
 
 __global__ void __launch_bounds__(256) k_ccl_paint(int16_t *__restrict__ img, const int *__restrict__ L, int H, int W,
