@@ -50,7 +50,7 @@
 #define AGG_EDGE_LIKE_ROW(G) ((G) == 32)
 #define AGG_UNROLL 12      // pixel-times per loop iteration: a multiple of SLOTS, ENS, PPS and the prefetch depths
 #ifndef AGG_PUB
-#define AGG_PUB 8          // publish cross-band progress every AGG_PUB pixels
+#define AGG_PUB 8          // publish cross-band progress every AGG_PUB pixels (a single frame in flight: every AGG_PPS)
 #endif
 #ifndef AGG_L2PF
 #define AGG_L2PF 32        // cross-band L2 prefetch distance (pixels ahead of the cp.async front), 0 = off
@@ -76,6 +76,7 @@ struct AggArgs {
     uint32_t one;          // == 1 (an opaque multiplier: x * one + y stays an IMAD on the FMA pipe)
     uint32_t k16;          // == 65536, likewise (x * k16 + y instead of a PRMT / shift on the ALU pipe)
     int uniq, invalid16;
+    int pubmask;           // publish progress when (pixels done & pubmask) < AGG_PPS
     int slack;             // extra producer lead a starving band waits for (0 when one frame is in flight)
 };
 
@@ -656,7 +657,7 @@ __global__ void __launch_bounds__(NGRP *G + (NV ? 32 : 0)) k_sweep(const __grid_
             cta_barrier();
             if (producer && lane == 0) {
                 const int done = t - lag_last;   // pixels of the last row finished before this barrier
-                if (done > 0 && done < W1 && (done % AGG_PUB) < AGG_PPS) st_release(prog + band, (unsigned)done);
+                if (done > 0 && done < W1 && (done & a.pubmask) < AGG_PPS) st_release(prog + band, (unsigned)done);
             }
         }
         cta_barrier();
@@ -829,6 +830,8 @@ int svb_launch_aggregate(svb_context *ctx, const SgbmPlan &pl, char *ws, size_t 
     a.k16 = 65536;
     a.uniq = pl.p.uniquenessRatio;
     a.invalid16 = pl.invalid16;
+    a.pubmask = AGG_PUB - 1;
+    if (const char *e = getenv("SVB_SWEEP_PUB")) a.pubmask = atoi(e) - 1;   // tuning hook (power of two)
     a.slack = 0;   // (hysteresis for starving bands: measured no better than 0 since the edges are L2-prefetched)
     if (const char *e = getenv("SVB_SWEEP_SLACK")) a.slack = atoi(e);   // tuning hook
     const int pad = pl.Dp != pl.D;
