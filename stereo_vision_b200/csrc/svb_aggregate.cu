@@ -4,26 +4,31 @@
 // Design: ONE sweep kernel computes four path directions per pass as a wavefront.
 //   * a "row-group" of G lanes owns one image row; each lane holds E=2*NR consecutive disparities as NR packed
 //     s16x2 registers.  The group walks its row in x; the horizontal path lives in registers.
-//   * row v trails row v-1 by two pixels, so the three vertical/diagonal predecessors (u-1,u,u+1 of row v-1) are
-//     already available.  Inside a CTA (a band of NGRP rows) they travel through a 4-slot shared-memory ring whose
-//     slot index is the step number mod 4 — the step loop is unrolled by 4, so every ring address is an
-//     immediate.  Each ring vector is preceded by a 16-byte pad holding P2, which is the d=-1 / d=D halo of the
-//     recurrence, so the neighbour taps are plain unconditional LDS.
+//   * the CTA (a band of NGRP rows) advances AGG_PPS = 2 pixels per bar.sync; row v trails row v-1 by AGG_LAG = 3
+//     pixels, so the three vertical/diagonal predecessors (u-1,u,u+1 of row v-1) of both pixels are at least one
+//     barrier old.  They travel through an AGG_SLOTS = 6-slot shared-memory ring per row whose slot index is the
+//     pixel-time mod 6 — the loop is unrolled by AGG_UNROLL = 12 pixel-times, so every ring address is an immediate.
+//     Each ring vector is preceded by a 16-byte pad holding P2, which is the d=-1 / d=D halo of the recurrence, so the
+//     neighbour taps are plain unconditional LDS.
 //   * between bands the three states travel through a global edge buffer.  A dedicated DMA warp per CTA polls the
-//     producer band's progress counter (ld.acquire), pulls the edge vectors EDGE_PF pixels ahead into an 8-slot
-//     "row -1" ring with cp.async, and publishes this band's own progress (st.release) — all off the compute
-//     warps' critical path.  Bands take tickets in launch order, so a band only ever waits for one that is
-//     already running (no deadlock, no cooperative launch).
-//   * C (and S in pass 2) are prefetched PFD pixels ahead into registers; C is read exactly once per pass,
+//     producer band's progress counter (relaxed loads, see ld_acquire), prefetches the edge vectors into L2 AGG_L2PF
+//     pixels ahead, pulls them into the "row -1" ring with cp.async, and publishes this band's own progress
+//     (st.release) — all off the compute warps' critical path.  Bands take tickets in band-major order, so a band only
+//     ever waits for one that is already running (no deadlock, no cooperative launch).
+//   * C, S and the edge stream are addressed as one pointer per unrolled iteration + compile-time offsets (Dp = G*E and
+//     the sweep direction are template constants); the pointers are not clamped to the row (SVB_SWEEP_MARGIN).
+//     C (and S in pass 2) are prefetched PFD pixels ahead into registers; C is read exactly once per pass,
 //     S written once (pass 1) / read once (pass 2): the four directions of a pass accumulate in registers.
 //   * the loop body is branch-free: out-of-grid predecessors are zero vectors selected by pointer, inactive
-//     steps compute on clamped addresses with their stores predicated off.
+//     pixel-times store into a trash row, global stores are predicated.
 //   * recurrence in normalised form: with Lc = min(Lprev - minLprev, P2),
-//         L(d) = C(d) + min(Lc(d), min(Lc(d-1), Lc(d+1)) + P1)          (== cv2's formula)
-//     -> per packed pair: PRMT, VIMNMX, VIADDMNMX, IADD, IADD(S), 1/2 VIMNMX3, VIADDMNMX(normalise+clamp).
-//   * pass 2 (reverse sweep) adds its four directions to S from pass 1 and selects the disparity in-register;
-//     the per-pixel scalars (min S, best d, second-best S, subpixel taps) are parked one pixel per lane and the
-//     scalar tail (uniqueness test, subpixel division, disp2 scatter, store) runs lane-parallel every G pixels.
+//         L(d) = C(d) + min(Lc(d), Lc(d-1) + P1, Lc(d+1) + P1)          (== cv2's formula)
+//     -> per packed pair: 1.25 PRMT, VIMNMX3, VIADDMNMX (normalise+clamp) on the ALU pipe; the +P1, +C and the add
+//        into S are IMADs on the FMA pipe; directions are finished in pairs (finish_pair).
+//   * pass 2 (reverse sweep) adds its four directions to S from pass 1; the selection of a pixel (winner, second
+//     best, subpixel taps) runs one pixel-time later from a shared-memory copy of S (select), its three scalars are
+//     parked in shared memory, and the scalar tail (uniqueness test, subpixel division, disp2 scatter, store) runs
+//     lane-parallel every 24 pixels (flush).
 #include "svb_common.cuh"
 #include <stdlib.h>
 
