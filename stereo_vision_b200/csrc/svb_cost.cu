@@ -3,8 +3,8 @@
 //
 //   k_planes : u8 images -> per-pixel BT operands, already widened to packed s16x2 so the cost kernel's inner
 //              loop is pure DPX/VIADD work:
-//                left  LP[y][pl][xi]          = uint4 { (u,u), (255-u,255-u), (u0,u0), (255-u1,255-u1) }
-//                right RP[y][pl][arr 4][w < Wr] = uint4: elements j = w..w+7 of the int16 arrays V, 255-V, V0, 255-V1
+//                left  LP[y][pl][xi]          = uint4 { (u,u), (255-u,255-u), (u0+255,u0+255), (255-u1,255-u1) }
+//                right RP[y][pl][arr 3][w < Wr] = uint4: elements j = w..w+7 of the int16 arrays V, V0, 255-V1
 //                                               stored REVERSED in x (index j = W-1-x): the 8 disparities of any
 //                                               window w are one aligned LDG.128, and consecutive windows (consecutive
 //                                               lanes of the cost kernel) are consecutive 16-byte words.
@@ -15,6 +15,8 @@
 // BT in biased form (no negative operands):  with a' = 255-a,
 //   c0+255 = max(255, u+v1', v0+u')   c1+255 = max(255, v+u1', u0+v')   cost = max(min(X,Y)-255, 0)
 //   X = max(u+v1', v0+u'), Y = max(v+u1', u0+v')            -> 2 VIADD + 2 VIADDMNMX + 1 VIMNMX + 1 VIADDMNMX.RELU
+//   (u0+v' is evaluated as (u0+255) - v with the 255 folded into the stored left operand: the right image needs no
+//   255-V array)
 #include "svb_common.cuh"
 #include <algorithm>
 #include <cstdlib>
@@ -54,8 +56,8 @@ __global__ void __launch_bounds__(PLANES_THREADS) k_planes(const uint8_t *__rest
 {
     extern __shared__ __align__(16) unsigned char psm[];
     const int Wa = Wr + 16;                                   // staged array length (8 zeros in front, >= 8 behind)
-    int16_t *A = reinterpret_cast<int16_t *>(psm);            // [4][Wa]
-    uint8_t *pvL = psm + (size_t)4 * Wa * 2;                  // [W]
+    int16_t *A = reinterpret_cast<int16_t *>(psm);            // [3][Wa]: V, V0, 255-V1
+    uint8_t *pvL = psm + (size_t)3 * Wa * 2;                  // [W]
     uint8_t *pvR = pvL + ((W + 15) & ~15);                    // [W]
     const int y = blockIdx.x, b = blockIdx.y, tid = threadIdx.x;
     const int NPL = 2 * C;
@@ -80,7 +82,7 @@ __global__ void __launch_bounds__(PLANES_THREADS) k_planes(const uint8_t *__rest
             int lo, hi;
             const int p = pvL[x];
             bt_triplet(x > 0 ? pvL[x - 1] : 0, p, x < W - 1 ? pvL[x + 1] : 0, x > 0, x < W - 1, lo, hi);
-            LP[((size_t)y * NPL + pl) * W1 + xi] = make_uint4(dup16(p), dup16(255 - p), dup16(lo), dup16(255 - hi));
+            LP[((size_t)y * NPL + pl) * W1 + xi] = make_uint4(dup16(p), dup16(255 - p), dup16(lo + 255), dup16(255 - hi));
         }
         // right operands, reversed: staged index j + 8 <-> x = W-1-j
         for (int i = tid; i < Wa; i += PLANES_THREADS) {
@@ -92,13 +94,13 @@ __global__ void __launch_bounds__(PLANES_THREADS) k_planes(const uint8_t *__rest
                 bt_triplet(x > 0 ? pvR[x - 1] : 0, p, x < W - 1 ? pvR[x + 1] : 0, x > 0, x < W - 1, lo, hi);
                 v = p; vn = 255 - p; v0 = lo; v1n = 255 - hi;
             }
-            A[i] = (int16_t)v; A[Wa + i] = (int16_t)vn; A[2 * Wa + i] = (int16_t)v0; A[3 * Wa + i] = (int16_t)v1n;
+            A[i] = (int16_t)v; A[Wa + i] = (int16_t)v0; A[2 * Wa + i] = (int16_t)v1n;
         }
         __syncthreads();
         // one uint4 per window (8 consecutive reversed elements), consecutive windows by consecutive threads:
         // 5 aligned words from the staged array, shifted by half a word for odd windows
-        uint4 *outp = reinterpret_cast<uint4 *>(RP) + ((size_t)y * NPL + pl) * 4 * Wr;
-        for (int i = tid; i < 4 * Wr; i += PLANES_THREADS) {
+        uint4 *outp = reinterpret_cast<uint4 *>(RP) + ((size_t)y * NPL + pl) * 3 * Wr;
+        for (int i = tid; i < 3 * Wr; i += PLANES_THREADS) {
             const int a = i / Wr, w = i - a * Wr;
             const uint32_t *src = reinterpret_cast<const uint32_t *>(A + (size_t)a * Wa) + ((w + 8) >> 1);
             const uint32_t sel = (w & 1) ? 0x5432u : 0x3210u;
@@ -113,7 +115,7 @@ int svb_launch_planes(const SgbmPlan &pl, const uint8_t *left, const uint8_t *ri
                       char *ws, size_t ws_stride, int B, cudaStream_t st)
 {
     dim3 grid(pl.H, B);
-    const size_t smem = (size_t)4 * (pl.Wr + 16) * 2 + 2 * (size_t)((pl.W + 15) & ~15);
+    const size_t smem = (size_t)3 * (pl.Wr + 16) * 2 + 2 * (size_t)((pl.W + 15) & ~15);
     static size_t configured = 0;
     if (smem > 48 * 1024 && smem > configured) {
         SVB_CUDA_CHECK(cudaFuncSetAttribute(k_planes, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -133,7 +135,7 @@ int svb_launch_planes(const SgbmPlan &pl, const uint8_t *left, const uint8_t *ri
 // x = T0 - R + 8l + ci, ci in [0, NW).  Every window has exactly G cells, so phase 1 is perfectly balanced, and for a
 // fixed l the tile is a contiguous run of columns, which is all the box sums need.  Per input row r (clamped to the
 // image: cost-space border replication):
-//   phase 1: thread (ci, part) holds window ci's operands in registers (4 arrays x NPL planes, aligned LDG.128 from
+//   phase 1: thread (ci, part) holds window ci's operands in registers (3 arrays x NPL planes, aligned LDG.128 from
 //            copy w%8, prefetched one row ahead) and computes its CPT = G/NPART cells l = part*CPT.., parking the pixel
 //            costs in a double-buffered shared-memory row pix[ci][l] (column stride Dp+8: conflict-free).
 //   phase 2: lane l of column block cb owns CPB adjacent output columns of group l: running sum of the 2R+1
@@ -152,7 +154,7 @@ int svb_launch_planes(const SgbmPlan &pl, const uint8_t *left, const uint8_t *ri
 #endif
 
 template <int NPL>
-struct CostWindow { uint4 v[NPL][4]; };   // [plane][V, 255-V, V0, 255-V1]
+struct CostWindow { uint4 v[NPL][3]; };   // [plane][V, V0, 255-V1]
 
 // rb: this thread's window in copy w%8 of plane 0 / array 0 of the row; (plane, array) strides are CTA-uniform
 template <int NPL>
@@ -161,8 +163,8 @@ __device__ __forceinline__ void load_window(CostWindow<NPL> &cw, const char *__r
 #pragma unroll
     for (int pl = 0; pl < NPL; pl++)
 #pragma unroll
-        for (int a = 0; a < 4; a++)
-            cw.v[pl][a] = __ldg(reinterpret_cast<const uint4 *>(rb + (size_t)((pl * 4 + a) * arr_bytes)));
+        for (int a = 0; a < 3; a++)
+            cw.v[pl][a] = __ldg(reinterpret_cast<const uint4 *>(rb + (size_t)((pl * 3 + a) * arr_bytes)));
 }
 
 __device__ __forceinline__ uint32_t u4get(const uint4 &q, int i) { return i == 0 ? q.x : i == 1 ? q.y : i == 2 ? q.z : q.w; }
@@ -200,9 +202,9 @@ __device__ __forceinline__ void pix_cell(const CostWindow<NPL> &cw, const uint4 
     for (int pl = 0; pl < NPL; pl++) {
 #pragma unroll
         for (int i = 0; i < 4; i++) {
-            const uint32_t Bv = u4get(cw.v[pl][2], i) + Lw[pl].y;                         // v0 + (255-u)
-            const uint32_t X = __viaddmax_s16x2(Lw[pl].x, u4get(cw.v[pl][3], i), Bv);     // max(u + 255-v1, .)
-            const uint32_t Ev = Lw[pl].z + u4get(cw.v[pl][1], i);                         // u0 + (255-v)
+            const uint32_t Bv = u4get(cw.v[pl][1], i) + Lw[pl].y;                         // v0 + (255-u)
+            const uint32_t X = __viaddmax_s16x2(Lw[pl].x, u4get(cw.v[pl][2], i), Bv);     // max(u + 255-v1, .)
+            const uint32_t Ev = Lw[pl].z - u4get(cw.v[pl][0], i);                         // (u0+255) - v: no borrow
             const uint32_t Y = __viaddmax_s16x2(u4get(cw.v[pl][0], i), Lw[pl].w, Ev);     // max(v + 255-u1, .)
             uint32_t c = __viaddmax_s16x2_relu(__vmins2(X, Y), 0xFF01FF01u, 0u);          // max(min-255, 0)
             if (pl & 1) c = (c >> 2) & 0x3FFF3FFFu;
@@ -365,7 +367,7 @@ struct CostProducer {
         work = vmask != 0;
         sts0 = t.smem0 + (uint32_t)(ci * t.PS + l0 * 8) * 2u;
         arr_bytes = (uint32_t)a.Wr * 16u;                                 // one array of one plane: Wr windows
-        rrow_bytes = (size_t)NPL * 4 * arr_bytes;
+        rrow_bytes = (size_t)NPL * 3 * arr_bytes;
         rb0 = RP + (size_t)wld * 16;
         LPt = LP + xf;
         if (work) {
@@ -396,7 +398,7 @@ struct CostProducer {
             if (last) signal();
             if (work && (!last || r < t.r1)) {                            // next chunk's operands
                 const int rn = max(0, min(t.H - 1, last ? r + 1 : r)), chn = last ? 0 : ch + 1;
-                load_window<2>(cur, rb0 + (size_t)rn * rrow_bytes + (size_t)(chn * 8) * arr_bytes, arr_bytes);
+                load_window<2>(cur, rb0 + (size_t)rn * rrow_bytes + (size_t)(chn * 6) * arr_bytes, arr_bytes);
                 load_left(LA, LPt + ((size_t)rn * NPL + 2 * chn) * t.W1, t.W1, 0, vmask);
                 load_left(LB, LPt + ((size_t)rn * NPL + 2 * chn) * t.W1, t.W1, 2, vmask);
             }
