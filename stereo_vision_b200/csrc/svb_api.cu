@@ -131,7 +131,7 @@ int svb_make_plan(const svb_sgbm_params *raw, int H, int W, int ch, SgbmPlan *pl
     size_t off = 0;
     auto take = [&](size_t bytes) { size_t o = off; off = svb_align_up(off + std::max<size_t>(bytes, 16), 256); return o; };
     const size_t vol = (size_t)H * pl->W1 * pl->Dp * 2;
-    pl->off_lplanes = take((size_t)H * pl->nplanes * pl->W1 * 16);
+    pl->off_lplanes = take((size_t)H * pl->nplanes * pl->W1 * 4);   // [H][channel][W1] uint2 (one word per plane)
     pl->off_rplanes = take((size_t)H * pl->nplanes * 24 * (pl->Wr + 8) * 2 + 64);   // [H][plane][3 arrays][Wr windows] uint4 (fits: 48*Wr <= 48*(Wr+8))
     // the sweep kernels address C and S as running pointers that are not clamped to the row: their ramp-up /
     // ramp-down prefetches touch (never use) up to SVB_SWEEP_MARGIN bytes either side of each volume

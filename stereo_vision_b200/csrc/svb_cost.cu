@@ -3,7 +3,9 @@
 //
 //   k_planes : u8 images -> per-pixel BT operands, already widened to packed s16x2 so the cost kernel's inner
 //              loop is pure DPX/VIADD work:
-//                left  LP[y][pl][xi]          = uint4 { (u,u), (255-u,255-u), (u0+255,u0+255), (255-u1,255-u1) }
+//                left  LP[y][pl][xi]          = bytes (u, 255-u, u0, 255-u1) of plane pl of channel pl/2: LP[y][ch][xi] = uint2 {gradient, intensity};
+//                                               the cost kernel stages a row of them in shared memory and widens them
+//                                               to (u,u), (255-u,255-u), (u0+255,u0+255), (255-u1,255-u1) per cell
 //                right RP[y][pl][arr 3][w < Wr] = uint4: elements j = w..w+7 of the int16 arrays V, V0, 255-V1
 //                                               stored REVERSED in x (index j = W-1-x): the 8 disparities of any
 //                                               window w are one aligned LDG.128, and consecutive windows (consecutive
@@ -51,7 +53,7 @@ __device__ __forceinline__ uint32_t dup16(int v) { return (uint32_t)v * 0x10001u
 #define PLANES_THREADS 256
 __global__ void __launch_bounds__(PLANES_THREADS) k_planes(const uint8_t *__restrict__ left, const uint8_t *__restrict__ right,
                                                            int H, int W, int C, size_t pitch, size_t istride, int ftzero,
-                                                           int minX1, int W1, int Wr, uint4 *__restrict__ LP,
+                                                           int minX1, int W1, int Wr, uint32_t *__restrict__ LP,
                                                            int16_t *__restrict__ RP, size_t ws_stride)
 {
     extern __shared__ __align__(16) unsigned char psm[];
@@ -63,7 +65,7 @@ __global__ void __launch_bounds__(PLANES_THREADS) k_planes(const uint8_t *__rest
     const int NPL = 2 * C;
     left += (size_t)b * istride;
     right += (size_t)b * istride;
-    LP = reinterpret_cast<uint4 *>(reinterpret_cast<char *>(LP) + (size_t)b * ws_stride);
+    LP = reinterpret_cast<uint32_t *>(reinterpret_cast<char *>(LP) + (size_t)b * ws_stride);
     RP = reinterpret_cast<int16_t *>(reinterpret_cast<char *>(RP) + (size_t)b * ws_stride);
     const int yn = max(y - 1, 0), ys = min(y + 1, H - 1);
     const uint8_t *lc = left + (size_t)y * pitch, *ln = left + (size_t)yn * pitch, *ls = left + (size_t)ys * pitch;
@@ -82,7 +84,9 @@ __global__ void __launch_bounds__(PLANES_THREADS) k_planes(const uint8_t *__rest
             int lo, hi;
             const int p = pvL[x];
             bt_triplet(x > 0 ? pvL[x - 1] : 0, p, x < W - 1 ? pvL[x + 1] : 0, x > 0, x < W - 1, lo, hi);
-            LP[((size_t)y * NPL + pl) * W1 + xi] = make_uint4(dup16(p), dup16(255 - p), dup16(lo + 255), dup16(255 - hi));
+            // one word per column and plane; the two planes of a channel are the .x / .y of one uint2
+            LP[(((size_t)y * (NPL / 2) + (pl >> 1)) * W1 + xi) * 2 + (pl & 1)] =
+                (uint32_t)p | ((uint32_t)(255 - p) << 8) | ((uint32_t)lo << 16) | ((uint32_t)(255 - hi) << 24);
         }
         // right operands, reversed: staged index j + 8 <-> x = W-1-j
         for (int i = tid; i < Wa; i += PLANES_THREADS) {
@@ -122,7 +126,7 @@ int svb_launch_planes(const SgbmPlan &pl, const uint8_t *left, const uint8_t *ri
         configured = smem;
     }
     k_planes<<<grid, PLANES_THREADS, smem, st>>>(left, right, pl.H, pl.W, pl.ch, pitch, istride, pl.ftzero, pl.minX1,
-                                                 pl.W1, pl.Wr, (uint4 *)(ws + pl.off_lplanes),
+                                                 pl.W1, pl.Wr, (uint32_t *)(ws + pl.off_lplanes),
                                                  (int16_t *)(ws + pl.off_rplanes), ws_stride);
     SVB_CUDA_CHECK(cudaGetLastError());
     return SVB_OK;
@@ -144,9 +148,6 @@ int svb_launch_planes(const SgbmPlan &pl, const uint8_t *left, const uint8_t *ri
 //            (2R+1)-th row on it writes C[r-R][x][8l..8l+8), x = T0 + 8l + c.
 // The horizontal sums never touch HBM; C is written exactly once (2 B per pixel-disparity).
 #define COST_ROLE 256    // threads per role (phase 1 / phase 2)
-#ifndef COST_WS
-#define COST_WS 0        // 1: warp-specialised variant (512 threads); measured slower, kept for experiments
-#endif
 #define COST_CPB_MAX 8   // output columns per thread (phase 2)
 #define COST_CPT_MAX 8   // cells per thread (phase 1)
 #ifndef COST_P2_COLS
@@ -214,7 +215,7 @@ __device__ __forceinline__ void pix_cell(const CostWindow<NPL> &cw, const uint4 
 }
 
 struct CostArgs {
-    const uint4 *LP; const int16_t *RP; int16_t *Cv;
+    const uint2 *LP; const int16_t *RP; int16_t *Cv;
     int H, W1, Wr, Dp, D, G, jb0, NW, NPART, CPT, NCB, rows_per_seg, zrow;
     uint32_t cpad;
     size_t ws_stride;
@@ -300,60 +301,63 @@ __device__ __forceinline__ void cost_phase2_row(const CostP2 &q, int16_t *cout, 
                                   acc + h * NC);
 }
 
-// left-image operands of two cells (k0, k0+1) x two planes
-struct CostLeft { uint4 v[2][2]; };
-__device__ __forceinline__ void load_left(CostLeft &L, const uint4 *LPx, int W1, int k0, uint32_t vmask)
+// left operands: one word per column and plane (bytes u, 255-u, u0, 255-u1), widened to duplicated s16x2 per cell
+__device__ __forceinline__ uint4 widen_left(uint32_t w)
 {
-#pragma unroll
-    for (int c = 0; c < 2; c++)
-#pragma unroll
-        for (int pl = 0; pl < 2; pl++) L.v[c][pl] = ldg_nc_pred(LPx + (size_t)pl * W1 + 8 * (k0 + c), vmask >> (k0 + c) & 1);
+    return make_uint4(__byte_perm(w, 0u, 0x4040), __byte_perm(w, 0u, 0x4141), __byte_perm(w, 0u, 0x4242) + 0x00FF00FFu,
+                      __byte_perm(w, 0u, 0x4343));
 }
-__device__ __forceinline__ void cells2(const CostWindow<2> &cur, const CostLeft &L, uint32_t sts, int k0, uint32_t vmask,
-                                       bool accumulate)
+__device__ __forceinline__ uint2 lds64(uint32_t saddr)
 {
-#pragma unroll
-    for (int c = 0; c < 2; c++) {
-        uint32_t p[4];
-        pix_cell<2>(cur, L.v[c], p);
-        if (accumulate) {
-            const uint4 prev = lds128(sts + 16u * (k0 + c));     // in-bounds even when the cell is not valid
-            p[0] += prev.x; p[1] += prev.y; p[2] += prev.z; p[3] += prev.w;
-        }
-        sts128_pred(sts + 16u * (k0 + c), p, vmask >> (k0 + c) & 1);
-    }
+    uint2 v;
+    asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(saddr));
+    return v;
 }
-
-// named barriers (id 0 is __syncthreads): FULL[b] producers arrive / consumers wait, EMPTY[b] the reverse
-__device__ __forceinline__ void bar_sync(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
-__device__ __forceinline__ void bar_arrive(int id, int n) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(n) : "memory"); }
-#define COST_BAR_FULL 1    // +buffer
-#define COST_BAR_EMPTY 3   // +buffer
-#define COST_BAR_CONS 5
+__device__ __forceinline__ void cp_async8(uint32_t saddr, const void *gmem)
+{
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(saddr), "l"(gmem) : "memory");
+}
 
 struct CostTile {   // per-CTA geometry shared by both roles
-    int G, Dp, NW, TX, W1, H, PS, T0, ya, yb, r0, r1;
-    uint32_t smem0, pix_bytes;
+    int G, Dp, NW, TX, W1, H, PS, T0, ya, yb, r0, r1, NCOL;
+    uint32_t smem0, pix_bytes, left0, left_bytes;   // left0: staged left operands [2][NCH][NCOL] uint2
 };
 
 // ---- producer role (phase 1): window ci of the tile, cells l = l0 .. l0+CPT-1 ----
+// Left operands: the row's NCOL = NW + 8(G-1) columns x NCH channels are staged in shared memory one row ahead with
+// cp.async (8 bytes per column and channel); every cell reads its word pair with one LDS.64 and widens it.  No
+// left-operand register is live across cells and no global load sits on the cells' critical path (ptxas sinks
+// ld.global.nc to its first use when registers are short: the former register double buffer had no distance left).
 template <int NPL, int R>
 struct CostProducer {
     static constexpr int NCH = NPL / 2;
     // the window registers hold ONE channel (gradient + intensity plane) at a time; for 3-channel input the pixel
     // cost accumulates in the thread's own shared-memory cells, and the next chunk's operands load while one computes
     CostWindow<2> cur;
-    CostLeft LA, LB;   // left operands of cell pairs, fetched two pairs ahead (also across rows)
-    const uint4 *LPt;
+    const uint2 *LPb;          // this frame's left operands
     const char *rb0;
     size_t rrow_bytes;
-    uint32_t arr_bytes, sts0, vmask;
+    uint32_t arr_bytes, sts0, vmask, lds0;
+    int tid;
     bool work;
 
-    __device__ __forceinline__ void init(const CostArgs &a, const CostTile &t, int tid, int b)
+    // stage the left operands of image row rc into buffer lb (all threads; columns clamped to the image)
+    __device__ __forceinline__ void stage(const CostTile &t, int rc, int lb) const
+    {
+        const uint2 *src = LPb + (size_t)rc * NCH * t.W1;
+        const uint32_t dst = t.left0 + (uint32_t)lb * t.left_bytes;
+        for (int i = tid; i < NCH * t.NCOL; i += COST_ROLE) {
+            const int ch = i / t.NCOL, col = i - ch * t.NCOL;
+            const int x = min(max(t.T0 - R + col, 0), t.W1 - 1);
+            cp_async8(dst + 8u * (uint32_t)i, src + (size_t)ch * t.W1 + x);
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    }
+    __device__ __forceinline__ void init(const CostArgs &a, const CostTile &t, int tid_, int b)
     {
         static_assert(COST_CPT_MAX == 8, "phase 1 is written for 8 cells per thread");
-        const uint4 *LP = reinterpret_cast<const uint4 *>(reinterpret_cast<const char *>(a.LP) + (size_t)b * a.ws_stride);
+        tid = tid_;
+        LPb = reinterpret_cast<const uint2 *>(reinterpret_cast<const char *>(a.LP) + (size_t)b * a.ws_stride);
         const char *RP = reinterpret_cast<const char *>(a.RP) + (size_t)b * a.ws_stride;
         const int ci = tid % t.NW, part = tid / t.NW;
         const bool p1 = part < a.NPART;
@@ -366,43 +370,49 @@ struct CostProducer {
             if (p1 && k < a.CPT && (unsigned)(xf + 8 * k) < (unsigned)t.W1) vmask |= 1u << k;
         work = vmask != 0;
         sts0 = t.smem0 + (uint32_t)(ci * t.PS + l0 * 8) * 2u;
+        lds0 = t.left0 + 8u * (uint32_t)(ci + 8 * l0);                    // staged word pair of the first cell, channel 0
         arr_bytes = (uint32_t)a.Wr * 16u;                                 // one array of one plane: Wr windows
         rrow_bytes = (size_t)NPL * 3 * arr_bytes;
         rb0 = RP + (size_t)wld * 16;
-        LPt = LP + xf;
-        if (work) {
-            const int rc0 = max(0, min(t.H - 1, t.r0));
-            load_window<2>(cur, rb0 + (size_t)rc0 * rrow_bytes, arr_bytes);
-            load_left(LA, LPt + (size_t)rc0 * NPL * t.W1, t.W1, 0, vmask);
-            load_left(LB, LPt + (size_t)rc0 * NPL * t.W1, t.W1, 2, vmask);
-        }
+        const int rc0 = max(0, min(t.H - 1, t.r0));
+        stage(t, rc0, 0);
+        if (work) load_window<2>(cur, rb0 + (size_t)rc0 * rrow_bytes, arr_bytes);
+        asm volatile("cp.async.wait_group 0;" ::: "memory");             // made visible by the caller's __syncthreads
     }
-    // writes pix row r into buffer buf; `signal()` runs when the row is complete (before the next operands are fetched)
-    template <typename F>
-    __device__ __forceinline__ void row(const CostTile &t, int r, int buf, F signal)
+    // writes pix row r into pix buffer buf (it == r - r0: the staged left operands of row r sit in buffer it & 1)
+    __device__ __forceinline__ void row(const CostTile &t, int r, int buf)
     {
-        const int rc = max(0, min(t.H - 1, r));
+        const int it = r - t.r0;
+        if (r < t.r1) stage(t, max(0, min(t.H - 1, r + 1)), (it + 1) & 1);   // next row's left operands
         const uint32_t sts = sts0 + (uint32_t)buf * t.pix_bytes;
+        const uint32_t lds = lds0 + (uint32_t)(it & 1) * t.left_bytes;
 #pragma unroll 1
         for (int ch = 0; ch < NCH; ch++) {
             const bool last = ch + 1 == NCH;
-            if (work) {   // 8 cells in pairs; a pair's operands are always fetched right after a compute block
-                const uint4 *LPx = LPt + ((size_t)rc * NPL + 2 * ch) * t.W1;
-                cells2(cur, LA, sts, 0, vmask, ch > 0);
-                load_left(LA, LPx, t.W1, 4, vmask);
-                cells2(cur, LB, sts, 2, vmask, ch > 0);
-                load_left(LB, LPx, t.W1, 6, vmask);
-                cells2(cur, LA, sts, 4, vmask, ch > 0);
-                cells2(cur, LB, sts, 6, vmask, ch > 0);
+            if (work) {
+                const uint32_t la = lds + 8u * (uint32_t)(ch * t.NCOL);
+                uint2 w[COST_CPT_MAX];
+#pragma unroll
+                for (int k = 0; k < COST_CPT_MAX; k++) w[k] = lds64(la + 64u * k);   // cell k: 8 columns further (cells k >= CPT
+                                                                                     // read the slack behind the staged rows)
+#pragma unroll
+                for (int k = 0; k < COST_CPT_MAX; k++) {
+                    const uint4 Lw[2] = {widen_left(w[k].x), widen_left(w[k].y)};
+                    uint32_t p[4];
+                    pix_cell<2>(cur, Lw, p);
+                    if (ch > 0) {
+                        const uint4 prev = lds128(sts + 16u * k);        // in-bounds even when the cell is not valid
+                        p[0] += prev.x; p[1] += prev.y; p[2] += prev.z; p[3] += prev.w;
+                    }
+                    sts128_pred(sts + 16u * k, p, vmask >> k & 1);
+                }
             }
-            if (last) signal();
-            if (work && (!last || r < t.r1)) {                            // next chunk's operands
+            if (work && (!last || r < t.r1)) {                            // next chunk's window
                 const int rn = max(0, min(t.H - 1, last ? r + 1 : r)), chn = last ? 0 : ch + 1;
                 load_window<2>(cur, rb0 + (size_t)rn * rrow_bytes + (size_t)(chn * 6) * arr_bytes, arr_bytes);
-                load_left(LA, LPt + ((size_t)rn * NPL + 2 * chn) * t.W1, t.W1, 0, vmask);
-                load_left(LB, LPt + ((size_t)rn * NPL + 2 * chn) * t.W1, t.W1, 2, vmask);
             }
         }
+        asm volatile("cp.async.wait_group 0;" ::: "memory");             // next row's left operands landed (this thread's)
     }
 };
 
@@ -476,10 +486,9 @@ struct CostConsumer {
     }
 };
 
-// WS = false: every thread plays both roles, one __syncthreads per row (the pix row is double-buffered).
-// WS = true : warp-specialised, threads [0, COST_ROLE) produce, [COST_ROLE, 2*COST_ROLE) consume, named barriers.
-template <int NPL, int R, int GT, bool WS>   // GT: compile-time G (0 = runtime)
-__global__ void __launch_bounds__(WS ? 2 * COST_ROLE : COST_ROLE, 1) k_cost_fused(const __grid_constant__ CostArgs a)
+// Every thread plays both roles, one __syncthreads per row (the pix row and the staged left operands are double-buffered).
+template <int NPL, int R, int GT>   // GT: compile-time G (0 = runtime)
+__global__ void __launch_bounds__(COST_ROLE, 1) k_cost_fused(const __grid_constant__ CostArgs a)
 {
     constexpr int BS = 2 * R + 1;
     extern __shared__ __align__(16) unsigned char csm[];
@@ -487,45 +496,27 @@ __global__ void __launch_bounds__(WS ? 2 * COST_ROLE : COST_ROLE, 1) k_cost_fuse
     t.G = GT ? GT : a.G; t.Dp = t.G * 8;
     t.NW = a.NW; t.TX = t.NW - 2 * R; t.W1 = a.W1; t.H = a.H;
     t.PS = t.Dp + 8;                                                       // pix column stride (elements)
-    t.smem0 = (uint32_t)__cvta_generic_to_shared(csm);                     // pix [2][NW][PS], then ring [BS][TX][Dp]
+    t.smem0 = (uint32_t)__cvta_generic_to_shared(csm);                     // pix [2][NW][PS], ring [BS][TX][Dp], left
     t.pix_bytes = (uint32_t)(t.NW * t.PS) * 2u;
+    t.NCOL = t.NW + 8 * (t.G - 1);
+    t.left_bytes = (uint32_t)((NPL / 2) * t.NCOL) * 8u;
+    t.left0 = t.smem0 + 2u * t.pix_bytes + (uint32_t)(BS * t.TX * t.Dp) * 2u;
     t.T0 = blockIdx.x * t.TX - 8 * (t.G - 1);                              // x of output column 0 of group 0
     t.ya = blockIdx.y * a.rows_per_seg; t.yb = min(t.ya + a.rows_per_seg, t.H);
     t.r0 = t.ya - R; t.r1 = t.yb - 1 + R;
     const int b = blockIdx.z;
     const int nring = BS * t.TX * t.Dp / 8;   // ring starts at zero: "subtract the row that leaves the window" is unconditional
-    if (!WS) {
-        CostProducer<NPL, R> P;
-        CostConsumer<R> C;
-        for (int i = threadIdx.x; i < nring; i += COST_ROLE) sts128(C.ring0(t) + 16u * i, 0, 0, 0, 0);
-        P.init(a, t, threadIdx.x, b);
-        C.init(a, t, threadIdx.x, b);
-        for (int r = t.r0; r <= t.r1; r++) {
-            const int buf = (r - t.r0) & 1;
-            P.row(t, r, buf, [] {});
-            __syncthreads();
-            C.row(t, r, buf);
-        }
-    } else if (threadIdx.x < COST_ROLE) {
-        CostProducer<NPL, R> P;
-        P.init(a, t, threadIdx.x, b);
-        for (int r = t.r0; r <= t.r1; r++) {
-            const int it = r - t.r0, buf = it & 1;
-            if (it >= 2) bar_sync(COST_BAR_EMPTY + buf, 2 * COST_ROLE);    // consumers are done with row it-2
-            P.row(t, r, buf, [&] { bar_arrive(COST_BAR_FULL + buf, 2 * COST_ROLE); });
-        }
-    } else {
-        CostConsumer<R> C;
-        const int tid = threadIdx.x - COST_ROLE;
-        for (int i = tid; i < nring; i += COST_ROLE) sts128(C.ring0(t) + 16u * i, 0, 0, 0, 0);
-        bar_sync(COST_BAR_CONS, COST_ROLE);
-        C.init(a, t, tid, b);
-        for (int r = t.r0; r <= t.r1; r++) {
-            const int buf = (r - t.r0) & 1;
-            bar_sync(COST_BAR_FULL + buf, 2 * COST_ROLE);                  // row is in pix[buf]
-            C.row(t, r, buf);
-            if (r + 2 <= t.r1) bar_arrive(COST_BAR_EMPTY + buf, 2 * COST_ROLE);   // a producer will wait for it
-        }
+    CostProducer<NPL, R> P;
+    CostConsumer<R> C;
+    for (int i = threadIdx.x; i < nring; i += COST_ROLE) sts128(C.ring0(t) + 16u * i, 0, 0, 0, 0);
+    P.init(a, t, threadIdx.x, b);
+    C.init(a, t, threadIdx.x, b);
+    __syncthreads();                          // the first row's staged left operands are visible
+    for (int r = t.r0; r <= t.r1; r++) {
+        const int buf = (r - t.r0) & 1;
+        P.row(t, r, buf);
+        __syncthreads();
+        C.row(t, r, buf);
     }
 }
 
@@ -538,7 +529,11 @@ static CostGeom cost_geom(const SgbmPlan &pl)
     const size_t budget = budget_kb * 1024;
     g.NPART = std::max(1, Gc / 8);
     g.CPT = Gc / g.NPART;
-    auto bytes = [&](int nw) { return (size_t)2 * ((size_t)2 * nw * (pl.Dp + 8) + (size_t)BS * (nw - 2 * pl.R) * pl.Dp); };
+    auto bytes = [&](int nw) {   // pix [2][nw][Dp+8] + ring [BS][nw-2R][Dp] int16, staged left operands [2][NCH][nw+8(G-1)] uint2
+        return (size_t)2 * ((size_t)2 * nw * (pl.Dp + 8) + (size_t)BS * (nw - 2 * pl.R) * pl.Dp) +
+               (size_t)2 * (pl.nplanes / 2) * (nw + 8 * (Gc - 1)) * 8 +
+               (size_t)64 * (COST_CPT_MAX - g.CPT);   // slack: phase 1 reads 8 cells per thread even when CPT < 8
+    };
     // widest tile whose windows fit the CTA (phase 1: NW*NPART threads), whose column blocks of COST_CPB_MAX columns
     // fit it too (phase 2: ceil(TX/8)*G threads) and whose buffers fit shared memory
     int NW = std::min(COST_ROLE / g.NPART, pl.W1 + 8 * (Gc - 1) + 2 * pl.R);
@@ -557,14 +552,14 @@ static CostGeom cost_geom(const SgbmPlan &pl)
 template <int NPL, int R, int GT>
 static int launch_cost_fused(const SgbmPlan &pl, const CostGeom &g, char *ws, size_t ws_stride, int B, cudaStream_t st)
 {
-    auto kern = k_cost_fused<NPL, R, GT, COST_WS != 0>;
+    auto kern = k_cost_fused<NPL, R, GT>;
     static size_t configured = 0;
     if (g.smem > configured) {
         SVB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g.smem));
         configured = g.smem;
     }
     CostArgs a;
-    a.LP = (const uint4 *)(ws + pl.off_lplanes); a.RP = (const int16_t *)(ws + pl.off_rplanes); a.Cv = (int16_t *)(ws + pl.off_C);
+    a.LP = (const uint2 *)(ws + pl.off_lplanes); a.RP = (const int16_t *)(ws + pl.off_rplanes); a.Cv = (int16_t *)(ws + pl.off_C);
     a.H = pl.H; a.W1 = pl.W1; a.Wr = pl.Wr; a.Dp = pl.Dp; a.D = pl.D; a.G = pl.Dp / 8;
     a.jb0 = pl.W - 1 - pl.minX1 + pl.p.minDisparity;
     a.NW = g.NW; a.NPART = g.NPART; a.CPT = g.CPT; a.NCB = g.NCB; a.rows_per_seg = g.rows_per_seg;
@@ -572,7 +567,7 @@ static int launch_cost_fused(const SgbmPlan &pl, const CostGeom &g, char *ws, si
     a.cpad = (uint32_t)(32767 - pl.p.P2) * 0x10001u;
     a.ws_stride = ws_stride;
     dim3 grid(g.ntiles, g.nseg, B);
-    kern<<<grid, COST_WS ? 2 * COST_ROLE : COST_ROLE, g.smem, st>>>(a);
+    kern<<<grid, COST_ROLE, g.smem, st>>>(a);
     SVB_CUDA_CHECK(cudaGetLastError());
     return SVB_OK;
 }
