@@ -277,16 +277,21 @@ __device__ __forceinline__ void cost_phase2(const CostP2 &q, int kofs, int16_t *
         acc[k][0] += hs[0] - old[k].x; acc[k][1] += hs[1] - old[k].y;
         acc[k][2] += hs[2] - old[k].z; acc[k][3] += hs[3] - old[k].w;     // acc >= old per half: no borrow
         if (EMIT) {
-            uint32_t o[4] = {acc[k][0], acc[k][1], acc[k][2], acc[k][3]};
+            char *cp = reinterpret_cast<char *>(cout) + (size_t)k * q.Dp2;
             if (q.padded) {                                     // padded disparities carry CPAD (CTA-uniform branch)
+                uint32_t o[4];
 #pragma unroll
                 for (int j = 0; j < 4; j++) {
                     const uint32_t keep = ((q.lane * 8 + 2 * j < q.D) ? 0x0000FFFFu : 0u) |
                                           ((q.lane * 8 + 2 * j + 1 < q.D) ? 0xFFFF0000u : 0u);
-                    o[j] = (o[j] & keep) | (q.cpad & ~keep);
+                    o[j] = (acc[k][j] & keep) | (q.cpad & ~keep);
                 }
+                stg128_pred(cp, o[0], o[1], o[2], o[3], v);
+            } else {
+                // straight from the running sums: they are not written again before the next row's phase 2, so the
+                // store's source registers are not what the next row's phase 1 starts writing into
+                stg128_pred(cp, acc[k][0], acc[k][1], acc[k][2], acc[k][3], v);
             }
-            stg128_pred(reinterpret_cast<char *>(cout) + (size_t)k * q.Dp2, o[0], o[1], o[2], o[3], v);
         }
     }
 }
