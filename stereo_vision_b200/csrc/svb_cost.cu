@@ -194,22 +194,34 @@ __device__ __forceinline__ void sts128(uint32_t saddr, uint32_t a, uint32_t b, u
 }
 
 // BT cost of one cell (8 disparities = 4 packed registers) summed over the planes; plain `+` where no half can carry
+// The plain 32-bit adds / subtracts between packed halves (no carry or borrow by construction) are written as
+// x * one + y / x * mone + y with one == 1, mone == 0xFFFFFFFF opaque kernel arguments: ptxas keeps them as IMADs on
+// the FMA pipe instead of IADD3 / VIADD on the ALU pipe, which the packed min/max instructions need (COST_FMA).
+#ifndef COST_FMA
+#define COST_FMA 1
+#endif
+#if COST_FMA
+#define CADD(x, y, one) ((x) * (one) + (y))
+#define CSUB(y, x, mone) ((x) * (mone) + (y))          // y - x
+#else
+#define CADD(x, y, one) ((x) + (y))
+#define CSUB(y, x, mone) ((y) - (x))
+#endif
 template <int NPL>
-__device__ __forceinline__ void pix_cell(const CostWindow<NPL> &cw, const uint4 (&Lw)[NPL], uint32_t (&acc)[4])
+__device__ __forceinline__ void pix_cell(const CostWindow<NPL> &cw, const uint4 (&Lw)[NPL], uint32_t (&acc)[4],
+                                         uint32_t one, uint32_t mone)
 {
-#pragma unroll
-    for (int i = 0; i < 4; i++) acc[i] = 0;
 #pragma unroll
     for (int pl = 0; pl < NPL; pl++) {
 #pragma unroll
         for (int i = 0; i < 4; i++) {
-            const uint32_t Bv = u4get(cw.v[pl][1], i) + Lw[pl].y;                         // v0 + (255-u)
+            const uint32_t Bv = CADD(u4get(cw.v[pl][1], i), Lw[pl].y, one);               // v0 + (255-u)
             const uint32_t X = __viaddmax_s16x2(Lw[pl].x, u4get(cw.v[pl][2], i), Bv);     // max(u + 255-v1, .)
-            const uint32_t Ev = Lw[pl].z - u4get(cw.v[pl][0], i);                         // (u0+255) - v: no borrow
+            const uint32_t Ev = CSUB(Lw[pl].z, u4get(cw.v[pl][0], i), mone);              // (u0+255) - v: no borrow
             const uint32_t Y = __viaddmax_s16x2(u4get(cw.v[pl][0], i), Lw[pl].w, Ev);     // max(v + 255-u1, .)
             uint32_t c = __viaddmax_s16x2_relu(__vmins2(X, Y), 0xFF01FF01u, 0u);          // max(min-255, 0)
             if (pl & 1) c = (c >> 2) & 0x3FFF3FFFu;
-            acc[i] += c;
+            acc[i] = pl ? CADD(c, acc[i], one) : c;
         }
     }
 }
@@ -218,7 +230,11 @@ struct CostArgs {
     const uint2 *LP; const int16_t *RP; int16_t *Cv;
     int H, W1, Wr, Dp, D, G, jb0, NW, NPART, CPT, NCB, rows_per_seg, zrow;
     uint32_t cpad;
+    uint32_t one, mone;      // == 1, == 0xFFFFFFFF (opaque multipliers: x * one + y stays an IMAD on the FMA pipe)
     size_t ws_stride;
+    // phase-2 job of every thread: (column block << 8) | disparity group, 0xFFFF = none.  Threads are assigned so that
+    // the 8 lanes of a quarter warp own 8 consecutive groups at the SAME columns (see cost_jobs)
+    uint16_t job[COST_ROLE];
 };
 
 // phase 2 for one thread, one input row, NC adjacent output columns starting at tile column c0 + kofs.  One code path
@@ -231,7 +247,7 @@ struct CostP2 {
     uint32_t ringcell;   // ring slot cell of column c0 (shared address, + lane*16)
     uint32_t Dp2;
     int c0, cilo, cihi, lane, D;
-    uint32_t cmask, cpad;
+    uint32_t cmask, cpad, one, mone;
     bool live, padded;
 };
 __device__ __forceinline__ uint4 lds128_pred(uint32_t saddr, bool pred)
@@ -263,19 +279,27 @@ __device__ __forceinline__ void cost_phase2(const CostP2 &q, int kofs, int16_t *
 #pragma unroll
     for (int i = 0; i < NC + BS - 1; i++)
         pv[i] = lds128(q.pbs + (uint32_t)min(max(q.c0 + kofs + i, q.cilo), q.cihi) * q.PS2);
-    uint32_t hs[4] = {0, 0, 0, 0};
+    const uint32_t one = q.one, mone = q.mone;
+    uint32_t hs[4] = {pv[0].x, pv[0].y, pv[0].z, pv[0].w};
 #pragma unroll
-    for (int dx = 0; dx < BS; dx++) { hs[0] += pv[dx].x; hs[1] += pv[dx].y; hs[2] += pv[dx].z; hs[3] += pv[dx].w; }
+    for (int dx = 1; dx < BS; dx++) {
+        hs[0] = CADD(pv[dx].x, hs[0], one); hs[1] = CADD(pv[dx].y, hs[1], one);
+        hs[2] = CADD(pv[dx].z, hs[2], one); hs[3] = CADD(pv[dx].w, hs[3], one);
+    }
 #pragma unroll
     for (int k = 0; k < NC; k++) {
         if (k > 0) {   // slide the window one column to the right (per-half sums < 2^15: no carry / borrow)
-            hs[0] += pv[k + BS - 1].x - pv[k - 1].x; hs[1] += pv[k + BS - 1].y - pv[k - 1].y;
-            hs[2] += pv[k + BS - 1].z - pv[k - 1].z; hs[3] += pv[k + BS - 1].w - pv[k - 1].w;
+            hs[0] = CSUB(CADD(pv[k + BS - 1].x, hs[0], one), pv[k - 1].x, mone);
+            hs[1] = CSUB(CADD(pv[k + BS - 1].y, hs[1], one), pv[k - 1].y, mone);
+            hs[2] = CSUB(CADD(pv[k + BS - 1].z, hs[2], one), pv[k - 1].z, mone);
+            hs[3] = CSUB(CADD(pv[k + BS - 1].w, hs[3], one), pv[k - 1].w, mone);
         }
         const bool v = cmask >> k & 1;      // columns that are not real keep meaningless sums and store nothing
         sts128_pred4(ringcell + (uint32_t)k * q.Dp2, hs[0], hs[1], hs[2], hs[3], v);
-        acc[k][0] += hs[0] - old[k].x; acc[k][1] += hs[1] - old[k].y;
-        acc[k][2] += hs[2] - old[k].z; acc[k][3] += hs[3] - old[k].w;     // acc >= old per half: no borrow
+        acc[k][0] = CSUB(CADD(hs[0], acc[k][0], one), old[k].x, mone);
+        acc[k][1] = CSUB(CADD(hs[1], acc[k][1], one), old[k].y, mone);
+        acc[k][2] = CSUB(CADD(hs[2], acc[k][2], one), old[k].z, mone);
+        acc[k][3] = CSUB(CADD(hs[3], acc[k][3], one), old[k].w, mone);     // acc + hs >= old per half: no borrow
         if (EMIT) {
             char *cp = reinterpret_cast<char *>(cout) + (size_t)k * q.Dp2;
             if (q.padded) {                                     // padded disparities carry CPAD (CTA-uniform branch)
@@ -342,7 +366,7 @@ struct CostProducer {
     const uint2 *LPb;          // this frame's left operands
     const char *rb0;
     size_t rrow_bytes;
-    uint32_t arr_bytes, sts0, vmask, lds0;
+    uint32_t arr_bytes, sts0, vmask, lds0, one, mone;
     int tid;
     bool work;
 
@@ -361,7 +385,7 @@ struct CostProducer {
     __device__ __forceinline__ void init(const CostArgs &a, const CostTile &t, int tid_, int b)
     {
         static_assert(COST_CPT_MAX == 8, "phase 1 is written for 8 cells per thread");
-        tid = tid_;
+        tid = tid_; one = a.one; mone = a.mone;
         LPb = reinterpret_cast<const uint2 *>(reinterpret_cast<const char *>(a.LP) + (size_t)b * a.ws_stride);
         const char *RP = reinterpret_cast<const char *>(a.RP) + (size_t)b * a.ws_stride;
         const int ci = tid % t.NW, part = tid / t.NW;
@@ -404,10 +428,11 @@ struct CostProducer {
                 for (int k = 0; k < COST_CPT_MAX; k++) {
                     const uint4 Lw[2] = {widen_left(w[k].x), widen_left(w[k].y)};
                     uint32_t p[4];
-                    pix_cell<2>(cur, Lw, p);
+                    pix_cell<2>(cur, Lw, p, one, mone);
                     if (ch > 0) {
                         const uint4 prev = lds128(sts + 16u * k);        // in-bounds even when the cell is not valid
-                        p[0] += prev.x; p[1] += prev.y; p[2] += prev.z; p[3] += prev.w;
+                        p[0] = CADD(prev.x, p[0], one); p[1] = CADD(prev.y, p[1], one);
+                        p[2] = CADD(prev.z, p[2], one); p[3] = CADD(prev.w, p[3], one);
                     }
                     sts128_pred(sts + 16u * k, p, vmask >> k & 1);
                 }
@@ -436,7 +461,8 @@ struct CostConsumer {
     __device__ __forceinline__ void init(const CostArgs &a, const CostTile &t, int tid, int b)
     {
         int16_t *Cv = reinterpret_cast<int16_t *>(reinterpret_cast<char *>(a.Cv) + (size_t)b * a.ws_stride);
-        const int lane = tid % t.G, cb = tid / t.G;
+        const unsigned job = a.job[tid];
+        const int lane = job & 0xFF, cb = job >> 8;                        // cb == 0xFF (>= NCB): no phase-2 work
         const int c0 = cb * COST_CPB_MAX;
         const int xl = t.T0 + 8 * lane;                                    // x of output column 0 of this lane
         uint32_t cmask = 0;
@@ -447,7 +473,7 @@ struct CostConsumer {
         q.PS2 = (uint32_t)t.PS * 2u; q.Dp2 = Dp2;
         q.c0 = c0; q.lane = lane; q.D = a.D;
         q.cilo = min(max(R - xl, 0), t.NW - 1); q.cihi = min(max(t.W1 - 1 - xl + R, 0), t.NW - 1);
-        q.cmask = cmask; q.cpad = a.cpad; q.padded = a.D != t.Dp;
+        q.cmask = cmask; q.cpad = a.cpad; q.padded = a.D != t.Dp; q.one = a.one; q.mone = a.mone;
         pix0 = t.smem0 + (uint32_t)lane * 16u;
         ringcell0 = ring0(t) + (uint32_t)(c0 * t.Dp + lane * 8) * 2u;
         slot_bytes = (uint32_t)t.TX * Dp2;
@@ -526,6 +552,36 @@ __global__ void __launch_bounds__(COST_ROLE, 1) k_cost_fused(const __grid_consta
 }
 
 struct CostGeom { int NW, TX, NPART, CPT, NCB, ntiles, rows_per_seg, nseg; size_t smem; };
+
+// Phase-2 ownership.  Job (l, cb) = disparity group l, output columns x = T0 + 8*(l + cb) + k, k < 8.  Jobs with the
+// same s = l + cb and consecutive l write 16-byte pieces that are contiguous in C (same pixel, consecutive groups), so
+// the jobs are handed to threads in runs of 8 consecutive l of one s: a quarter warp then stores one contiguous 128-byte
+// run per column instead of 8 pieces in 8 different lines (tid % G / tid / G made every lane of a warp hit its own
+// 128-byte line: 32 L1 tag lookups per STG.128).  Full runs first (they stay aligned to quarter warps, which also keeps
+// every LDS.128 / STS.128 of phase 2 conflict-free: the shared-memory address is 16*l + const mod 128), ragged ends
+// of the parallelogram last.
+#ifndef COST_JOBMAP
+#define COST_JOBMAP 1
+#endif
+static void cost_jobs(int G, int NCB, uint16_t *job)
+{
+    int n = 0;
+    for (int i = 0; i < COST_ROLE; i++) job[i] = 0xFFFF;
+#if COST_JOBMAP
+    for (int pass = 0; pass < 2; pass++)            // pass 0: full runs of 8, pass 1: the rest
+        for (int s = 0; s <= G + NCB - 2; s++) {
+            const int lo = std::max(0, s - NCB + 1), hi = std::min(G - 1, s);
+            for (int l0 = lo; l0 <= hi; l0 += 8) {
+                const int len = std::min(8, hi - l0 + 1);
+                if ((len == 8) != (pass == 0)) continue;
+                for (int l = l0; l < l0 + len && n < COST_ROLE; l++) job[n++] = (uint16_t)(((s - l) << 8) | l);
+            }
+        }
+#else
+    for (int cb = 0; cb < NCB; cb++)
+        for (int l = 0; l < G && n < COST_ROLE; l++) job[n++] = (uint16_t)((cb << 8) | l);
+#endif
+}
 static CostGeom cost_geom(const SgbmPlan &pl)
 {
     CostGeom g;
@@ -570,7 +626,9 @@ static int launch_cost_fused(const SgbmPlan &pl, const CostGeom &g, char *ws, si
     a.NW = g.NW; a.NPART = g.NPART; a.CPT = g.CPT; a.NCB = g.NCB; a.rows_per_seg = g.rows_per_seg;
     a.zrow = pl.p.mode == 3 ? pl.H - pl.R : pl.H;
     a.cpad = (uint32_t)(32767 - pl.p.P2) * 0x10001u;
+    a.one = 1u; a.mone = 0xFFFFFFFFu;
     a.ws_stride = ws_stride;
+    cost_jobs(a.G, g.NCB, a.job);
     dim3 grid(g.ntiles, g.nseg, B);
     kern<<<grid, COST_ROLE, g.smem, st>>>(a);
     SVB_CUDA_CHECK(cudaGetLastError());
