@@ -96,6 +96,17 @@ int svb_filter_speckles_s16(svb_context *ctx, int16_t *img, int H, int W, size_t
                             size_t stride_elems, int newVal, int maxSpeckleSize, int maxDiff, int32_t *labels_ws,
                             size_t labels_ws_elems, void *stream);
 
+/* No-allocation variant of svb_filter_speckles_s16.  It has NO counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid it).  The label workspace is a static device array inside libsvb.so
+ * (SVB_NOALLOC_SPECKLE_MAX_PIXELS * 8 bytes = 16 MiB, held by every GPU that loads the library until exit); the call
+ * allocates nothing.  B*H*W must be <= SVB_NOALLOC_SPECKLE_MAX_PIXELS, otherwise SVB_ERR_WORKSPACE.  All calls on a
+ * device share the array: calls that overlap on the GPU (different streams without ordering) race.  The first call
+ * per device resolves the array's address (cudaGetSymbolAddress): make it once before starting a graph capture. */
+#define SVB_NOALLOC_SPECKLE_MAX_PIXELS (1 << 21)   /* e.g. one 1920x1080 map, or 2 x 1280x720 */
+int svb_filter_speckles_s16_noalloc(svb_context *ctx, int16_t *img, int H, int W, size_t pitch_elems, int B,
+                                    size_t stride_elems, int newVal, int maxSpeckleSize, int maxDiff, void *stream);
+
 /* ---- rectification ---- */
 /* K[9], dist[ndist] (ndist in 0,4,5,8,12,14), R[9] (NULL = I), P33[9] = P[:3,:3] (NULL = K): HOST pointers
  * (calibration-time scalars).  mapx/mapy: device f32 [H][W]. */

@@ -30,7 +30,7 @@ EXPORTS = [
     "svb_filter_speckles_s16", "svb_init_undistort_rectify_map", "svb_remap_u8", "svb_reproject_to_3d",
     "svb_box_median_depth", "svb_set_timing", "svb_sgbm_last_stage_ms", "svb_measure_packed_alu_peak",
     "svb_undistort_points", "svb_triangulate_points", "svb_bgr2gray_u8", "svb_init_undistort_rectify_map_fixed",
-    "svb_remap_u8_fixed",
+    "svb_remap_u8_fixed", "svb_filter_speckles_s16_noalloc",
 ]
 
 _lib = None
@@ -57,6 +57,7 @@ def load():
     lib.svb_sgbm_debug_stages.argtypes = [vp, C.POINTER(SgbmParams), vp, vp, i32, i32, i32, sz, vp, vp, vp, vp]
     lib.svb_median3_s16.argtypes = [vp, vp, vp, i32, i32, sz, i32, sz, vp]
     lib.svb_filter_speckles_s16.argtypes = [vp, vp, i32, i32, sz, i32, sz, i32, i32, i32, vp, sz, vp]
+    lib.svb_filter_speckles_s16_noalloc.argtypes = [vp, vp, i32, i32, sz, i32, sz, i32, i32, i32, vp]
     lib.svb_init_undistort_rectify_map.argtypes = [vp, vp, vp, i32, vp, vp, i32, i32, vp, vp, vp]
     lib.svb_remap_u8.argtypes = [vp, vp, i32, i32, i32, sz, sz, vp, vp, vp, i32, i32, sz, sz, i32, vp]
     lib.svb_init_undistort_rectify_map_fixed.argtypes = lib.svb_init_undistort_rectify_map.argtypes

@@ -269,3 +269,50 @@ extern "C" int svb_filter_speckles_s16(svb_context *ctx, int16_t *img, int H, in
     return svb_launch_speckle(img, H, W, pitch_elems, stride_elems, B, newVal, maxSpeckleSize, maxDiff, labels_ws,
                               (size_t)2 * H * W, (cudaStream_t)stream);
 }
+
+// ---- filterSpeckles without any allocation (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: CUDA graph capture, tight serving loops) ----
+// The label / component-size scratch of the CCL kernels lives in a file-scope device array of fixed size: every GPU
+// that loads libsvb.so holds SVB_NOALLOC_SPECKLE_MAX_PIXELS * 8 bytes (16 MiB) until the process exits.  The array's
+// name is only a host-side stand-in here: the device address is resolved once per device, with that device current,
+// by cudaGetSymbolAddress, and that pointer is what the kernels get.
+static __device__ __align__(256) int32_t g_speckle_scratch[2 * (size_t)SVB_NOALLOC_SPECKLE_MAX_PIXELS];
+
+#define SVB_MAX_DEVICES 64
+static int32_t *g_speckle_scratch_ptr[SVB_MAX_DEVICES];   // per device, 0 = not resolved yet
+#include <mutex>
+static std::mutex g_speckle_scratch_mu;
+
+static int speckle_scratch_for_device(int device, int32_t **out)
+{
+    SVB_REQUIRE(device >= 0 && device < SVB_MAX_DEVICES, SVB_ERR_INVALID, "filter_speckles_noalloc: device %d out of range", device);
+    std::lock_guard<std::mutex> lk(g_speckle_scratch_mu);
+    if (!g_speckle_scratch_ptr[device]) {
+        int32_t *p = nullptr;
+        SVB_CUDA_CHECK(cudaGetSymbolAddress((void **)&p, g_speckle_scratch));   // current device == `device` (caller)
+        SVB_REQUIRE(p != nullptr, SVB_ERR_CUDA, "filter_speckles_noalloc: cudaGetSymbolAddress returned a null pointer");
+        g_speckle_scratch_ptr[device] = p;
+    }
+    *out = g_speckle_scratch_ptr[device];
+    return SVB_OK;
+}
+
+extern "C" int svb_filter_speckles_s16_noalloc(svb_context *ctx, int16_t *img, int H, int W, size_t pitch_elems, int B,
+                                               size_t stride_elems, int newVal, int maxSpeckleSize, int maxDiff,
+                                               void *stream)
+{
+    SVB_REQUIRE(ctx && img, SVB_ERR_INVALID, "filter_speckles_noalloc: null argument");
+    SVB_REQUIRE(H > 0 && W > 0 && B > 0 && pitch_elems >= (size_t)W, SVB_ERR_INVALID, "filter_speckles_noalloc: bad size");
+    SVB_REQUIRE((size_t)H * W * B <= (size_t)SVB_NOALLOC_SPECKLE_MAX_PIXELS, SVB_ERR_WORKSPACE,
+                "filter_speckles_noalloc: B*H*W = %zu pixels exceeds the static scratch (SVB_NOALLOC_SPECKLE_MAX_PIXELS = %d); "
+                "use svb_filter_speckles_s16 with a caller-owned workspace",
+                (size_t)H * W * B, SVB_NOALLOC_SPECKLE_MAX_PIXELS);
+    SVB_CUDA_CHECK(cudaSetDevice(ctx->device));
+    int32_t *scratch;
+    int rc = speckle_scratch_for_device(ctx->device, &scratch);
+    if (rc) return rc;
+    // svb_launch_speckle clears the component-size half of the scratch on the stream and k_ccl_init writes every
+    // label, so nothing of the previous call's contents is read
+    return svb_launch_speckle(img, H, W, pitch_elems, stride_elems, B, newVal, maxSpeckleSize, maxDiff, scratch,
+                              (size_t)2 * H * W, (cudaStream_t)stream);
+}
