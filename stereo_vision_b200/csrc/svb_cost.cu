@@ -220,7 +220,13 @@ __device__ __forceinline__ void pix_cell(const CostWindow<NPL> &cw, const uint4 
             const uint32_t Ev = CSUB(Lw[pl].z, u4get(cw.v[pl][0], i), mone);              // (u0+255) - v: no borrow
             const uint32_t Y = __viaddmax_s16x2(u4get(cw.v[pl][0], i), Lw[pl].w, Ev);     // max(v + 255-u1, .)
             uint32_t c = __viaddmax_s16x2_relu(__vmins2(X, Y), 0xFF01FF01u, 0u);          // max(min-255, 0)
+#if COST_FMA
+            // c >> 2 per half (c <= 255 per half): c * 64 puts half h's bits 2..7 into byte 2h+1 — one IMAD on the FMA
+            // pipe + one PRMT instead of SHF + LOP3 on the ALU pipe
+            if (pl & 1) c = __byte_perm(c * (one << 6), 0u, 0x4341);
+#else
             if (pl & 1) c = (c >> 2) & 0x3FFF3FFFu;
+#endif
             acc[i] = pl ? CADD(c, acc[i], one) : c;
         }
     }
@@ -517,7 +523,31 @@ struct CostConsumer {
     }
 };
 
+// The row loop.  Between two barriers a thread owes phase 2 of row i (reads pix buffer i & 1) and phase 1 of row i+1
+// (writes the other buffer) in either order.  Warps w and w + 4 share a scheduler: the lower four run phase 2 first,
+// the upper four phase 1 first (their barrier sits between the two), so that every scheduler has one warp in the
+// ALU-pipe-heavy BT phase while the other is in the FMA-pipe / shared-memory-heavy box-sum phase (COST_DEPHASE).
+#ifndef COST_DEPHASE
+#define COST_DEPHASE 1
+#endif
+template <int NPL, int R>
+__device__ __forceinline__ void cost_rows(CostProducer<NPL, R> &P, CostConsumer<R> &C, const CostTile &t)
+{
+    const int n = t.r1 - t.r0 + 1;
+    const int late = (COST_DEPHASE && threadIdx.x >= COST_ROLE / 2) ? 1 : 0;
+    P.row(t, t.r0, 0);
+    for (int i = 0; i <= n; i++) {
+        if (!late) __syncthreads();
+        const int ic = i - late;                                  // phase 2 of row ic
+        if (ic >= 0 && ic < n) C.row(t, t.r0 + ic, ic & 1);
+        if (late) __syncthreads();
+        if (i + 1 < n) P.row(t, t.r0 + i + 1, (i + 1) & 1);
+    }
+}
+
 // Every thread plays both roles, one __syncthreads per row (the pix row and the staged left operands are double-buffered).
+// (Measured and not adopted: a second, mask-free instantiation of the row loop for tiles that lie wholly inside the
+// image — 105 instructions fewer per row in phase 2, but 254 registers and twice the code: 14.75 ms against 14.26.)
 template <int NPL, int R, int GT>   // GT: compile-time G (0 = runtime)
 __global__ void __launch_bounds__(COST_ROLE, 1) k_cost_fused(const __grid_constant__ CostArgs a)
 {
@@ -543,12 +573,7 @@ __global__ void __launch_bounds__(COST_ROLE, 1) k_cost_fused(const __grid_consta
     P.init(a, t, threadIdx.x, b);
     C.init(a, t, threadIdx.x, b);
     __syncthreads();                          // the first row's staged left operands are visible
-    for (int r = t.r0; r <= t.r1; r++) {
-        const int buf = (r - t.r0) & 1;
-        P.row(t, r, buf);
-        __syncthreads();
-        C.row(t, r, buf);
-    }
+    cost_rows<NPL, R>(P, C, t);
 }
 
 struct CostGeom { int NW, TX, NPART, CPT, NCB, ntiles, rows_per_seg, nseg; size_t smem; };
