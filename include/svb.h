@@ -20,8 +20,10 @@
  * Conventions: every function returns 0 on success, <0 on error (message: svb_last_error(), thread-local).
  * All data pointers are DEVICE pointers owned by the caller (e.g. torch tensors' data_ptr()); `stream` is a
  * cudaStream_t passed as void* (NULL = legacy default stream).  Nothing here allocates memory the caller
- * must free, except the context itself.  One context per (host thread, device); calls on one context are
- * not re-entrant.  There is no CPU fallback: without a CUDA device every compute call fails.
+ * must free, except the context itself.  One context per device is enough: StereoSGBM jobs on one context
+ * are serialised (host threads by a mutex while they enqueue; a job on another stream than the previous one
+ * first waits on the device for it), because they share the context's scheduler counters and cached workspace.
+ * There is no CPU fallback: without a CUDA device every compute call fails.
  */
 #ifndef SVB_H
 #define SVB_H
@@ -44,7 +46,7 @@ typedef struct svb_context svb_context;
  * values happens inside the library — see svb_sgbm_resolve_params. */
 typedef struct svb_sgbm_params {
     int32_t minDisparity, numDisparities, blockSize, P1, P2, disp12MaxDiff, preFilterCap, uniquenessRatio,
-        speckleWindowSize, speckleRange, mode; /* mode: 0 = MODE_SGBM (5 paths), 1 = MODE_HH (8 paths) */
+        speckleWindowSize, speckleRange, mode; /* mode: 0 = MODE_SGBM (5 paths), 1 = MODE_HH (8), 2 = MODE_SGBM_3WAY, 3 = MODE_HH4 (4) */
 } svb_sgbm_params;
 
 /* Geometry derived from params + image width (SURVEY.md §3.2.1 "Constants"). */

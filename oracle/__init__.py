@@ -213,3 +213,4 @@ def bgr2gray(img) -> np.ndarray:
     out = np.empty(img.shape[:2], dtype=np.uint8)
     lib().svo_bgr2gray(_p(img), C.c_int(out.size), _p(out))
     return out
+

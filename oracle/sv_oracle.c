@@ -94,8 +94,18 @@ static void bt_minmax(const uint8_t *p, int W, uint8_t *lo, uint8_t *hi)
  * Cost volume C[y][xi][d] (int16), xi in [0,width1), d in [0,D)   — SURVEY.md §3.2.2-3.2.3.
  * Caller allocates H*width1*D int16.  Returns 0, or <0 on bad geometry.
  */
+static int cost_volume_rows(const uint8_t *left, const uint8_t *right, int H, int W, int C, size_t pitch,
+                            const svo_params *praw, int y0, int y1, int16_t *Cvol);
 int svo_sgbm_cost_volume(const uint8_t *left, const uint8_t *right, int H, int W, int C, size_t pitch,
                          const svo_params *praw, int16_t *Cvol)
+{
+    return cost_volume_rows(left, right, H, W, C, pitch, praw, 0, H, Cvol);
+}
+/* Rows [y0, y1) of the cost volume (stored from row 0 of Cvol).  The block window is clamped to row y0 at the top
+ * and to the IMAGE's last row at the bottom: this is how MODE_SGBM_3WAY runs every stripe (probed on cv2 4.13.0);
+ * with y0 = 0, y1 = H it is the ordinary volume.  The Sobel / intensity planes always come from the whole image. */
+static int cost_volume_rows(const uint8_t *left, const uint8_t *right, int H, int W, int C, size_t pitch,
+                            const svo_params *praw, int y0, int y1, int16_t *Cvol)
 {
     svo_params p;
     svo_resolve_params(praw, &p);
@@ -122,12 +132,14 @@ int svo_sgbm_cost_volume(const uint8_t *left, const uint8_t *right, int H, int W
             }
         }
     }
+    const int b0 = y0, b1 = H;   /* box clamp range */
+    const int py0 = imax(b0, y0 - r), py1 = imin(b1, y1 + r);
     size_t rowsz = (size_t)width1 * D;
     int16_t *pix = malloc(sizeof(int16_t) * rowsz * H);
     int16_t *hs = malloc(sizeof(int16_t) * rowsz * H);
     if (!pix || !hs) { free(Lp); free(Rp); free(pix); free(hs); return -2; }
 #pragma omp parallel for schedule(static)
-    for (int y = 0; y < H; y++) {
+    for (int y = py0; y < py1; y++) {
         int16_t *prow = pix + (size_t)y * rowsz;
         memset(prow, 0, sizeof(int16_t) * rowsz);
         for (int pl = 0; pl < nplanes; pl++) {
@@ -152,7 +164,7 @@ int svo_sgbm_cost_volume(const uint8_t *left, const uint8_t *right, int H, int W
     }
     /* horizontal box sum with clamp in cost space */
 #pragma omp parallel for schedule(static)
-    for (int y = 0; y < H; y++) {
+    for (int y = py0; y < py1; y++) {
         const int16_t *prow = pix + (size_t)y * rowsz;
         int16_t *hrow = hs + (size_t)y * rowsz;
         for (int xi = 0; xi < width1; xi++)
@@ -164,18 +176,18 @@ int svo_sgbm_cost_volume(const uint8_t *left, const uint8_t *right, int H, int W
     }
     /* vertical box sum with clamp */
 #pragma omp parallel for schedule(static)
-    for (int y = 0; y < H; y++) {
-        int16_t *crow = Cvol + (size_t)y * rowsz;
+    for (int y = y0; y < y1; y++) {
+        int16_t *crow = Cvol + (size_t)(y - y0) * rowsz;
         for (size_t i = 0; i < rowsz; i++) {
             int s = 0;
-            for (int dy = -r; dy <= r; dy++) s += hs[(size_t)iclamp(y + dy, 0, H - 1) * rowsz + i];
+            for (int dy = -r; dy <= r; dy++) s += hs[(size_t)iclamp(y + dy, b0, b1 - 1) * rowsz + i];
             crow[i] = (int16_t)s; /* wraps like cv2's int16 cost type if bs>=15 */
         }
     }
     /* MODE_HH4 (cv2 4.13.0, probed: tests/golden/make_golden.py mode-3 cases): rows whose block window leaves the
      * image at the bottom (y + r > H-1) never get a cost — the volume stays 0 there. */
     if (p.mode == 3 && r > 0)
-        for (int y = imax(H - r, 0); y < H; y++) memset(Cvol + (size_t)y * rowsz, 0, rowsz * sizeof(int16_t));
+        for (int y = imax(H - r, y0); y < y1; y++) memset(Cvol + (size_t)(y - y0) * rowsz, 0, rowsz * sizeof(int16_t));
     free(Lp); free(Rp); free(pix); free(hs);
     return 0;
 }
@@ -286,7 +298,15 @@ int svo_sgbm_aggregate(const int16_t *Cvol, int H, int W1, int D, int P1, int P2
 }
 
 /* SURVEY.md §3.2.5 — WTA, uniqueness, subpixel, disp2 scatter, LR check; one image. */
+static void select_impl(const int16_t *S, int H, int W, int W1, int D, const svo_params *p, int three_way, int16_t *disp);
 void svo_sgbm_select(const int16_t *S, int H, int W, int W1, int D, const svo_params *p /*resolved*/, int16_t *disp)
+{
+    select_impl(S, H, W, W1, D, p, 0, disp);
+}
+/* three_way: MODE_SGBM_3WAY's selection (cv2 4.13.0, probed with tests/golden/make_golden_3way.py) differs from the
+ * other modes' in two details: the winner among equal minima (8-lane SIMD search, see below) and the uniqueness test
+ * (a precomputed integer threshold, skipped altogether when uniquenessRatio == 0). */
+static void select_impl(const int16_t *S, int H, int W, int W1, int D, const svo_params *p, int three_way, int16_t *disp)
 {
     const int minD = p->minDisparity, maxD = minD + D;
     const int minX1 = imax(maxD, 0), maxX1 = W + imin(minD, 0);
@@ -307,9 +327,24 @@ void svo_sgbm_select(const int16_t *S, int H, int W, int W1, int D, const svo_pa
                 int minS = SVO_MAX_COST, bestD = -1;
                 for (int d = 0; d < D; d++)
                     if (Sp[d] < minS) { minS = Sp[d]; bestD = d; }
+                if (three_way && bestD >= 0) {
+                    /* the winner is searched with 8-lane SIMD: every lane (d mod 8) keeps the LAST d that attains its
+                     * minimum, then the smallest such d among the lanes holding the global minimum wins */
+                    const int NL = 8;
+                    int best = -1;
+                    for (int j = 0; j < NL && j < D; j++) {
+                        int last = -1;
+                        for (int d = j; d < D; d += NL)
+                            if (Sp[d] == minS) last = d;
+                        if (last >= 0 && (best < 0 || last < best)) best = last;
+                    }
+                    bestD = best;
+                }
                 int d;
                 for (d = 0; d < D; d++)
-                    if ((int)Sp[d] * (100 - uniq) < minS * 100 && abs(bestD - d) > 1) break;
+                    if (three_way) {   /* S(d) <= floor(minS * 100 / (100 - uniq)), and no test at all for uniq == 0 */
+                        if (uniq > 0 && (int)Sp[d] <= (minS * 100) / (100 - uniq) && abs(bestD - d) > 1) break;
+                    } else if ((int)Sp[d] * (100 - uniq) < minS * 100 && abs(bestD - d) > 1) break;
                 if (d < D) continue;
                 if (bestD < 0) {
                     /* all costs saturated: cv2 proceeds with bestD=-1 (x2 = x+1-minD ...). Mirror: */
@@ -403,18 +438,32 @@ int svo_filter_speckles_s16(int16_t *img, int H, int W, int newVal, int maxSpeck
     return 0;
 }
 
+static void sgbm_3way_raw(const uint8_t *left, const uint8_t *right, int H, int W, int C, size_t pitch,
+                          const svo_params *praw, int16_t *disp_raw);
 /* Whole StereoSGBM.compute(): planes -> C -> S -> select -> median3 -> speckle.    */
 int svo_sgbm_compute(const uint8_t *left, const uint8_t *right, int H, int W, int C, size_t pitch,
                      const svo_params *praw, int16_t *disp)
 {
     svo_params p;
     svo_resolve_params(praw, &p);
-    if (p.mode != 0 && p.mode != 1 && p.mode != 3) return -3;
+    if (p.mode < 0 || p.mode > 3) return -3;
     const int minD = p.minDisparity, D = p.numDisparities, maxD = minD + D;
     const int minX1 = imax(maxD, 0), maxX1 = W + imin(minD, 0), W1 = maxX1 - minX1;
     if (D <= 0) return -1;
-    if (W - maxD <= p.blockSize / 2 && 0) return -1;
     if (W1 <= 0) return -1;
+    if (p.mode == 2) {
+        const int stripe = (H + 3) / 4;
+        if (p.blockSize / 2 + 1 + (int)ceil(0.1 * stripe) > stripe) return -3;
+        int16_t *raw = malloc((size_t)H * W * sizeof(int16_t));
+        if (!raw) return -2;
+        sgbm_3way_raw(left, right, H, W, C, pitch, praw, raw);
+        svo_median3_s16(raw, H, W, disp);
+        if (p.speckleWindowSize > 0)
+            svo_filter_speckles_s16(disp, H, W, (minD - 1) * SVO_DISP_SCALE, p.speckleWindowSize,
+                                    SVO_DISP_SCALE * p.speckleRange);
+        free(raw);
+        return 0;
+    }
     size_t vol = (size_t)H * W1 * D;
     int16_t *Cvol = malloc(vol * sizeof(int16_t)), *S = malloc(vol * sizeof(int16_t));
     int16_t *tmp = malloc((size_t)H * W * sizeof(int16_t));
@@ -428,6 +477,52 @@ int svo_sgbm_compute(const uint8_t *left, const uint8_t *right, int H, int W, in
         svo_filter_speckles_s16(disp, H, W, (minD - 1) * SVO_DISP_SCALE, p.speckleWindowSize,
                                 SVO_DISP_SCALE * p.speckleRange);
     free(Cvol); free(S); free(tmp);
+    return 0;
+}
+
+/* MODE_SGBM_3WAY (cv2 4.13.0, probed — tests/golden/make_golden_3way.py): the image is cut into 4 row stripes of
+ * ceil(H/4) rows; stripe n > 0 starts `overlap` = blockSize/2 + 1 + ceil(0.1 * stripe) rows early and only its own
+ * rows are kept.  Inside a stripe: block sums clamped to the stripe's first row at the top (and to the image at the
+ * bottom), three paths — from the left, from above (restarted at the stripe's first row) and from the right — with the
+ * ordinary recurrence, then the 3-way selection (select_impl).  Images so short that overlap > stripe behave
+ * differently in cv2 (not modelled: svo_sgbm_compute returns -3 there, and so does the engine). */
+static void sgbm_3way_raw(const uint8_t *left, const uint8_t *right, int H, int W, int C, size_t pitch,
+                          const svo_params *praw, int16_t *disp_raw)
+{
+    svo_params p;
+    svo_resolve_params(praw, &p);
+    const int minD = p.minDisparity, D = p.numDisparities, maxD = minD + D;
+    const int minX1 = imax(maxD, 0), maxX1 = W + imin(minD, 0), W1 = maxX1 - minX1;
+    const int nstripes = 4;
+    const int stripe = (H + nstripes - 1) / nstripes;
+    const int overlap = p.blockSize / 2 + 1 + (int)ceil(0.1 * stripe);
+    for (int n = 0; n < nstripes; n++) {
+        const int ys = n == 0 ? 0 : imax(imin(n * stripe - overlap, H), 0);
+        const int ye = n == nstripes - 1 ? H : imin((n + 1) * stripe, H);
+        const int keep0 = n == 0 ? 0 : imin(n * stripe, H);
+        if (ye <= ys || keep0 >= ye) continue;
+        const int hs = ye - ys;
+        size_t vol = (size_t)hs * W1 * D;
+        int16_t *Cvol = malloc(vol * sizeof(int16_t)), *S = malloc(vol * sizeof(int16_t));
+        int16_t *tmp = malloc((size_t)hs * W * sizeof(int16_t));
+        cost_volume_rows(left, right, H, W, C, pitch, praw, ys, ye, Cvol);
+        svo_sgbm_aggregate_mask(Cvol, hs, W1, D, p.P1, p.P2, 0x15, S);   /* left, up, right predecessors */
+        select_impl(S, hs, W, W1, D, &p, 1, tmp);
+        memcpy(disp_raw + (size_t)keep0 * W, tmp + (size_t)(keep0 - ys) * W, (size_t)(ye - keep0) * W * sizeof(int16_t));
+        free(Cvol); free(S); free(tmp);
+    }
+}
+
+/* debug tap: rows [ys, ye) of the cost volume with 3-way clamping, and the 3-path S of that stripe */
+int svo_3way_stripe_debug(const uint8_t *left, const uint8_t *right, int H, int W, int C, size_t pitch,
+                          const svo_params *praw, int ys, int ye, int16_t *Cvol, int16_t *S)
+{
+    svo_params p;
+    svo_resolve_params(praw, &p);
+    const int minD = p.minDisparity, D = p.numDisparities, maxD = minD + D;
+    const int minX1 = imax(maxD, 0), maxX1 = W + imin(minD, 0), W1 = maxX1 - minX1;
+    cost_volume_rows(left, right, H, W, C, pitch, praw, ys, ye, Cvol);
+    svo_sgbm_aggregate_mask(Cvol, ye - ys, W1, D, p.P1, p.P2, 0x15, S);
     return 0;
 }
 

@@ -136,11 +136,13 @@ class StereoRig:
         with torch.cuda.device(self.device):
             return self.matcher.compute_batch(L, R) if batched else self.matcher.compute(L, R)
 
-    def box_depth(self, left, right, boxes, rectified=False):
-        """Median depth (and XYZ of it) of each detector box of the LEFT rectified view: the dense replacement for
-        the reference's centre-point triangulation."""
+    def box_depth(self, left, right, boxes, rectified=False, box_image=None):
+        """Median depth Z of each detector box of the LEFT rectified view: the dense replacement for the reference's
+        centre-point triangulation.  For a batch of frames `box_image` (int32, one frame index per box) is required."""
         disp = self.disparity(left, right, rectified)
-        return api.box_median_depth(disp, self.Q, boxes, minDisparity=self.matcher.getMinDisparity())
+        if disp.dim() == 3 and box_image is None:
+            raise ValueError("box_depth on a batch of frames needs box_image (the frame index of every box)")
+        return api.box_median_depth(disp, self.Q, boxes, minDisparity=self.matcher.getMinDisparity(), box_image=box_image)
 
     def triangulate(self, left_pts, right_pts, rectified_frame=False):
         """Batched 3-D positions of matched detections, (N,2) pixel coordinates in the ORIGINAL images.

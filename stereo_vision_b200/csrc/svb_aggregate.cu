@@ -11,7 +11,7 @@
 //     Each ring vector is preceded by a 16-byte pad holding P2, which is the d=-1 / d=D halo of the recurrence, so the
 //     neighbour taps are plain unconditional LDS.
 //   * between bands the three states travel through a global edge buffer.  A dedicated DMA warp per CTA polls the
-//     producer band's progress counter (relaxed loads, see ld_acquire), prefetches the edge vectors into L2 AGG_L2PF
+//     producer band's progress counter (relaxed loads + one acquire fence per advance, see ld_relaxed), prefetches the edge vectors into L2 AGG_L2PF
 //     pixels ahead, pulls them into the "row -1" ring with cp.async, and publishes this band's own progress
 //     (st.release) — all off the compute warps' critical path.  Bands take tickets in band-major order, so a band only
 //     ever waits for one that is already running (no deadlock, no cooperative launch).
@@ -87,14 +87,16 @@ struct AggArgs {
 };
 
 // Progress poll.  A relaxed (L1-bypassing) load, not ld.acquire: ptxas lowers every gpu-scope acquire/fence to
-// LDG + CCTL.IVALL, i.e. an invalidation of the SM's whole L1 on every poll.  The data the flag guards is only ever
-// read with cp.async.cg (L2, bypasses L1) issued after the loop exit in program order, so no stale line can be hit.
-__device__ __forceinline__ unsigned ld_acquire(const unsigned *p)
+// LDG + CCTL.IVALL, i.e. an invalidation of the SM's whole L1 on every poll.  The acquire side of the hand-off is one
+// fence_acquire() each time the known progress ADVANCES (at most once per AGG_PUB pixels, not once per poll), issued
+// before the cp.async.cg reads of the vectors that progress value guards.
+__device__ __forceinline__ unsigned ld_relaxed(const unsigned *p)
 {
     unsigned v;
     asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
     return v;
 }
+__device__ __forceinline__ void fence_acquire() { asm volatile("fence.acq_rel.gpu;" ::: "memory"); }
 __device__ __forceinline__ void st_release(unsigned *p, unsigned v)
 {
     asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
@@ -622,25 +624,29 @@ __global__ void __launch_bounds__(NGRP *G + (NV ? 32 : 0)) k_sweep(const __grid_
 #ifdef EXP_NOPOLL
         known = (unsigned)W1;
 #endif
-        if (consumer) pending = ld_acquire(prog_in);
+        if (consumer) pending = ld_relaxed(prog_in);
         for (int t = 0; t < nsteps; t += AGG_PPS) {
             // this iteration runs alongside the compute lanes' pixel-times t-PPS..t-1 and prepares t..t+PPS-1,
             // in which row 0 reads pixels < t+PPS+1
             const int need = min(t + AGG_PPS + 1, W1);
             if (consumer) {
+                const unsigned known0 = known;
                 known = max(known, pending);
-                if (known < (unsigned)W1) pending = ld_acquire(prog_in);
+                if (known < (unsigned)W1) pending = ld_relaxed(prog_in);
 #ifdef EXP_HARNESS
                 if ((int)known < need && lane == 0) { atomicAdd(&g_spin[0], 1ull); }
                 { long long c0 = clock64();
 #endif
                 if ((int)known < need) {   // starving: wait until the producer is a.slack pixels further (hysteresis:
                     const int target = min(need + a.slack, W1);   // equal-speed bands would otherwise re-starve at once)
-                    while ((int)known < target) known = ld_acquire(prog_in);
+                    while ((int)known < target) known = ld_relaxed(prog_in);
                 }
 #ifdef EXP_HARNESS
                   if (lane == 0) atomicAdd(&g_spin[1], (unsigned long long)(clock64() - c0)); }
                 if (lane == 0) atomicAdd(&g_spin[2], 1ull);
+#endif
+#ifndef AGG_NOFENCE
+                if (known != known0) fence_acquire();   // orders the vector reads below after the flag read
 #endif
                 constexpr int EPF = AGG_EDGE_LIKE_ROW(G) ? AGG_SLOTS - AGG_PPS - 2 : AGG_EPF;
                 const int limit = min(min(t + 1 + EPF, W1), (int)known);
@@ -745,11 +751,9 @@ static int launch_sweep_t(const AggArgs &a, int ngrid, cudaStream_t st)
     constexpr int PFD = NR == 4 ? (PASS2 ? AGG_PFD2 : 4) : 2;   // C prefetch depth in pixels (pass 2 is short of registers)
     const size_t smem = SweepSmem<NGRP, NV, PASS2>::bytes(a.Dp, 2 * NR);
     auto kern = k_sweep<NR, G, NGRP, NV, PASS2, SAFE, PAD, PFD>;
-    static size_t configured = 0;
-    if (smem > configured) {
-        SVB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = smem;
-    }
+    // the opt-in is per device and per function; setting it on every launch is cheap and stays correct with several
+    // devices / host threads in one process
+    SVB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     kern<<<ngrid, NGRP * G + (NV ? 32 : 0), smem, st>>>(a);
     SVB_CUDA_CHECK(cudaGetLastError());
     return SVB_OK;
@@ -837,9 +841,7 @@ int svb_launch_aggregate(svb_context *ctx, const SgbmPlan &pl, char *ws, size_t 
     a.uniq = pl.p.uniquenessRatio;
     a.invalid16 = pl.invalid16;
     a.pubmask = AGG_PUB - 1;
-    if (const char *e = getenv("SVB_SWEEP_PUB")) a.pubmask = atoi(e) - 1;   // tuning hook (power of two)
     a.slack = 0;   // (hysteresis for starving bands: measured no better than 0 since the edges are L2-prefetched)
-    if (const char *e = getenv("SVB_SWEEP_SLACK")) a.slack = atoi(e);   // tuning hook
     const int pad = pl.Dp != pl.D;
     const int NR = pl.E / 2;
     // pass 1: left, up-left, up, up-right

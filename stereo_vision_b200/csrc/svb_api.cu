@@ -40,6 +40,9 @@ extern "C" int svb_create(int device_id, svb_context **out)
     c->tickets = nullptr;
     c->timing = 0;
     c->ev_valid = 0;
+    c->job_valid = 0;
+    c->job_stream = nullptr;
+    cudaEventCreateWithFlags(&c->job_done, cudaEventDisableTiming);
     for (int i = 0; i <= SVB_NUM_STAGES; i++) cudaEventCreate(&c->ev[i]);
     e = cudaMalloc(&c->tickets, 16 * sizeof(unsigned));
     if (e != cudaSuccess) {
@@ -58,6 +61,7 @@ extern "C" int svb_destroy(svb_context *ctx)
     if (ctx->ws) cudaFree(ctx->ws);
     if (ctx->tickets) cudaFree(ctx->tickets);
     for (int i = 0; i <= SVB_NUM_STAGES; i++) cudaEventDestroy(ctx->ev[i]);
+    cudaEventDestroy(ctx->job_done);
     delete ctx;
     return SVB_OK;
 }
@@ -191,6 +195,20 @@ static int get_workspace(svb_context *ctx, size_t need, void *user_ws, size_t us
     return SVB_OK;
 }
 
+// Begin / end of a job that uses the context's tickets and (possibly) its cached workspace: see svb_context::mu.
+static int job_begin(svb_context *ctx, cudaStream_t st)
+{
+    if (ctx->job_valid && ctx->job_stream != st) SVB_CUDA_CHECK(cudaStreamWaitEvent(st, ctx->job_done, 0));
+    return SVB_OK;
+}
+static int job_end(svb_context *ctx, cudaStream_t st)
+{
+    SVB_CUDA_CHECK(cudaEventRecord(ctx->job_done, st));
+    ctx->job_stream = st;
+    ctx->job_valid = 1;
+    return SVB_OK;
+}
+
 static int run_front(svb_context *ctx, const SgbmPlan &pl, const uint8_t *left, const uint8_t *right, size_t pitch,
                      size_t istride, int B, char *ws, cudaStream_t st)
 {
@@ -214,8 +232,10 @@ extern "C" int svb_sgbm_compute(svb_context *ctx, const svb_sgbm_params *raw, co
                 "sgbm_compute: pitch smaller than a row");
     SVB_CUDA_CHECK(cudaSetDevice(ctx->device));
     cudaStream_t st = (cudaStream_t)stream;
+    std::lock_guard<std::mutex> lock(ctx->mu);
     char *ws;
     if ((rc = get_workspace(ctx, pl.per_frame_bytes * (size_t)B, ws_user, ws_bytes, &ws))) return rc;
+    if ((rc = job_begin(ctx, st))) return rc;
 #define SVB_MARK(i) do { if (ctx->timing) cudaEventRecord(ctx->ev[i], st); } while (0)
     ctx->ev_valid = 0;
     SVB_MARK(0);
@@ -239,7 +259,7 @@ extern "C" int svb_sgbm_compute(svb_context *ctx, const svb_sgbm_params *raw, co
             return rc;
     SVB_MARK(6);
     if (ctx->timing) ctx->ev_valid = 1;
-    return SVB_OK;
+    return job_end(ctx, st);
 }
 
 // Per-stage device times (ms) of the last svb_sgbm_compute on this context, measured with CUDA events recorded
@@ -271,17 +291,16 @@ extern "C" int svb_sgbm_debug_stages(svb_context *ctx, const svb_sgbm_params *ra
     if (rc) return rc;
     SVB_CUDA_CHECK(cudaSetDevice(ctx->device));
     cudaStream_t st = (cudaStream_t)stream;
+    std::lock_guard<std::mutex> lock(ctx->mu);
     char *ws;
     if ((rc = get_workspace(ctx, pl.per_frame_bytes, nullptr, 0, &ws))) return rc;
+    if ((rc = job_begin(ctx, st))) return rc;
     if ((rc = run_front(ctx, pl, left, right, pitch_bytes, 0, 1, ws, st))) return rc;
     const size_t vol = (size_t)H * pl.W1 * pl.Dp * 2;
     if (Cvol) SVB_CUDA_CHECK(cudaMemcpyAsync(Cvol, ws + pl.off_C, vol, cudaMemcpyDeviceToDevice, st));
     if (Svol || disp_raw) {
-        if (Svol) {
-            // S after pass 1 only is what the volume holds; run pass 1 + a selection-free copy for mode 0/1:
-            // for the tap we want the FINAL S, which pass 2 keeps in registers — so tap pass-1 S here and
-            // let the test add the remaining directions' contribution through disp_raw parity instead.
-        }
+        // the volume holds S after pass 1 only (pass 2 keeps the final S in registers): that is what Svol taps; the
+        // remaining directions are checked through disp_raw
         if ((rc = svb_launch_aggregate(ctx, pl, ws, pl.per_frame_bytes, 1, 3, st))) return rc;
         if (Svol) SVB_CUDA_CHECK(cudaMemcpyAsync(Svol, ws + pl.off_S, vol, cudaMemcpyDeviceToDevice, st));
         if (disp_raw) {
@@ -289,5 +308,5 @@ extern "C" int svb_sgbm_debug_stages(svb_context *ctx, const svb_sgbm_params *ra
             SVB_CUDA_CHECK(cudaMemcpyAsync(disp_raw, ws + pl.off_dtmp, (size_t)H * W * 2, cudaMemcpyDeviceToDevice, st));
         }
     }
-    return SVB_OK;
+    return job_end(ctx, st);
 }

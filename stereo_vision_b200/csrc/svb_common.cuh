@@ -5,6 +5,7 @@
 #include <stdio.h>
 #include <stdarg.h>
 #include <string.h>
+#include <mutex>
 
 #include "../../include/svb.h"
 
@@ -39,6 +40,13 @@ struct svb_context {
     void *ws;          // grow-only cached workspace
     size_t ws_bytes;
     unsigned int *tickets;  // device counters for the sweep scheduler
+    // One StereoSGBM job owns the tickets / progress counters / workspace at a time.  Host threads are serialised by
+    // `mu` while they enqueue; a job enqueued on a different stream than the previous one first waits (on the device)
+    // for the event recorded behind the previous job, so overlapping calls are ordered instead of corrupting each other.
+    std::mutex mu;
+    cudaEvent_t job_done;
+    cudaStream_t job_stream;
+    int job_valid;
     int timing;             // record per-stage events in svb_sgbm_compute
     cudaEvent_t ev[SVB_NUM_STAGES + 1];
     int ev_valid;

@@ -120,11 +120,8 @@ int svb_launch_planes(const SgbmPlan &pl, const uint8_t *left, const uint8_t *ri
 {
     dim3 grid(pl.H, B);
     const size_t smem = (size_t)3 * (pl.Wr + 16) * 2 + 2 * (size_t)((pl.W + 15) & ~15);
-    static size_t configured = 0;
-    if (smem > 48 * 1024 && smem > configured) {
+    if (smem > 48 * 1024)   // per device and function: set on every launch (cheap), correct with several devices
         SVB_CUDA_CHECK(cudaFuncSetAttribute(k_planes, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = smem;
-    }
     k_planes<<<grid, PLANES_THREADS, smem, st>>>(left, right, pl.H, pl.W, pl.ch, pitch, istride, pl.ftzero, pl.minX1,
                                                  pl.W1, pl.Wr, (uint32_t *)(ws + pl.off_lplanes),
                                                  (int16_t *)(ws + pl.off_rplanes), ws_stride);
@@ -611,8 +608,7 @@ static CostGeom cost_geom(const SgbmPlan &pl)
 {
     CostGeom g;
     const int Gc = pl.Dp / 8, BS = 2 * pl.R + 1;
-    static const size_t budget_kb = getenv("SVB_COST_SMEM_KB") ? atoi(getenv("SVB_COST_SMEM_KB")) : 226;
-    const size_t budget = budget_kb * 1024;
+    const size_t budget = (size_t)226 * 1024;
     g.NPART = std::max(1, Gc / 8);
     g.CPT = Gc / g.NPART;
     auto bytes = [&](int nw) {   // pix [2][nw][Dp+8] + ring [BS][nw-2R][Dp] int16, staged left operands [2][NCH][nw+8(G-1)] uint2
@@ -639,11 +635,7 @@ template <int NPL, int R, int GT>
 static int launch_cost_fused(const SgbmPlan &pl, const CostGeom &g, char *ws, size_t ws_stride, int B, cudaStream_t st)
 {
     auto kern = k_cost_fused<NPL, R, GT>;
-    static size_t configured = 0;
-    if (g.smem > configured) {
-        SVB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g.smem));
-        configured = g.smem;
-    }
+    SVB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g.smem));
     CostArgs a;
     a.LP = (const uint2 *)(ws + pl.off_lplanes); a.RP = (const int16_t *)(ws + pl.off_rplanes); a.Cv = (int16_t *)(ws + pl.off_C);
     a.H = pl.H; a.W1 = pl.W1; a.Wr = pl.Wr; a.Dp = pl.Dp; a.D = pl.D; a.G = pl.Dp / 8;

@@ -52,6 +52,12 @@ class HostPipeline:
         with torch.cuda.device(self.dev):
             main = torch.cuda.current_stream()
             if self.L[s] is None or self.L[s].shape != left_h.shape:
+                if self.used[s]:
+                    # the old slot buffers may still be read by the copy-out stream / written by the copy-in stream:
+                    # let the allocating stream wait for both before the caching allocator can reuse that memory
+                    main.wait_event(self.ev_out[s])
+                    main.wait_event(self.ev_in[s])
+                    self.used[s] = False
                 self.L[s] = torch.empty(left_h.shape, dtype=torch.uint8, device=d)
                 self.R[s] = torch.empty(left_h.shape, dtype=torch.uint8, device=d)
                 self.D[s] = torch.empty(disp_h.shape, dtype=torch.int16, device=d)

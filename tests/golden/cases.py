@@ -7,7 +7,7 @@ import numpy as np
 from stereo_vision_b200 import synth
 
 
-def sgbm_small_cases(n: int = 96, seed: int = 20261104, modes=(0, 1)):
+def sgbm_small_cases(n: int = 96, seed: int = 20261104, modes=(0, 1), hrange=(30, 44)):
     """Random sweep over the SURVEY.md §8c matrix; all in-contract (maxC + P2 <= 32767)."""
     rng = np.random.default_rng(seed)
     out = []
@@ -18,7 +18,7 @@ def sgbm_small_cases(n: int = 96, seed: int = 20261104, modes=(0, 1)):
         bs = int(rng.choice([1, 3, 5, 7, 9, 11])); cap = int(rng.choice([0, 31, 63])); uq = int(rng.choice([0, 5, 10, 15]))
         d12 = int(rng.choice([0, 1, 2, 3])); ch = int(rng.choice([1, 3]))
         kind = str(rng.choice(["smooth", "noise", "binary"]))
-        H = int(rng.integers(30, 44)); W = int(rng.integers(D + abs(minD) + 12, D + abs(minD) + 90))
+        H = int(rng.integers(*hrange)); W = int(rng.integers(D + abs(minD) + 12, D + abs(minD) + 90))
         P1 = int(rng.choice([0, 8 * ch * bs * bs])); P2 = int(rng.choice([0, 32 * ch * bs * bs]))
         sw = int(rng.choice([0, 20, 100])); sr = int(rng.choice([1, 2]))
         kw = dict(minDisparity=minD, numDisparities=D, blockSize=bs, P1=P1, P2=P2, disp12MaxDiff=d12,
@@ -36,6 +36,11 @@ def sgbm_small_cases(n: int = 96, seed: int = 20261104, modes=(0, 1)):
 def sgbm_hh4_cases(n: int = 40):
     """Same matrix for MODE_HH4 (mode 3)."""
     return sgbm_small_cases(n, seed=20261105, modes=(3,))
+
+
+def sgbm_3way_cases(n: int = 48):
+    """Same matrix for MODE_SGBM_3WAY (mode 2): taller images, so that the four row stripes and their overlaps matter."""
+    return sgbm_small_cases(n, seed=20261106, modes=(2,), hrange=(40, 90))
 
 
 def sgbm_inputs(case):
@@ -91,3 +96,20 @@ def post_inputs(seed=9):
 
 
 SPECKLE_PARAMS = [(20, 16), (100, 32), (16, 0), (5, 200)]
+
+
+# ---- round 2 (make_golden_r2.py) ----
+REF_V5_SIZE = (1080, 1920)   # (W, H): the calibrate_v5 cameras' principal point is ~ (550, 500); portrait 1080p
+
+
+def ref_v5_frame(seed=41):
+    """A random BGR frame of the fixture's size (smoothed so that bilinear weights matter)."""
+    W, H = REF_V5_SIZE
+    rng = np.random.default_rng(seed)
+    return np.ascontiguousarray(np.stack([synth._gauss_blur_u8(rng.integers(0, 256, (H, W), dtype=np.uint8))
+                                          for _ in range(3)], -1))
+
+
+def chain_c2_inputs(seed=2000):
+    """Raw (unrectified) 1280x720 BGR pair for the c2 pipeline chain."""
+    return synth.stereo_pair(720, 1280, 128, seed=seed, channels=3)

@@ -90,3 +90,84 @@ def test_sgbm_hh4_small_sweep_and_full_hash():
         full = json.load(f)
     L, R, kw = cases.full_inputs("c3")
     assert _sha(oracle.sgbm_compute(L, R, **dict(kw, mode=3))) == full["c3_hh4"]
+
+
+def _gdir():
+    import os
+    return os.path.join(os.path.dirname(__file__), "golden")
+
+
+def test_sgbm_3way_small_sweep_and_full_hashes():
+    """MODE_SGBM_3WAY (mode 2): 4 row stripes with restarted paths, 3 paths, the SIMD tie rule and
+    the integer uniqueness threshold of cv2's 3-way selection (make_golden_3way.py: thread-count independent)."""
+    import json
+    import os
+    g = np.load(os.path.join(_gdir(), "golden_3way.npz"))
+    for i, c in enumerate(cases.sgbm_3way_cases()):
+        L, R = cases.sgbm_inputs(c)
+        assert np.array_equal(oracle.sgbm_compute(L, R, **c["kw"]), g[f"w3_{i}"]), (i, c)
+    with open(os.path.join(_gdir(), "golden_3way_full.json")) as f:
+        full = json.load(f)
+    for name in ("c1", "c2"):
+        L, R, kw = cases.full_inputs(name)
+        assert _sha(oracle.sgbm_compute(L, R, **dict(kw, mode=2))) == full[f"{name}_3way"]
+    # images too short for the stripe overlap are outside the contract (cv2 behaves differently there)
+    z = np.zeros((12, 80), np.uint8)
+    with pytest.raises(ValueError):
+        oracle.sgbm_compute(z, z, numDisparities=16, blockSize=9, mode=2)
+
+
+@pytest.fixture(scope="module")
+def golden_r2():
+    import json
+    import os
+    with open(os.path.join(_gdir(), "golden_r2.json")) as f:
+        meta = json.load(f)
+    return meta, np.load(os.path.join(_gdir(), "golden_r2.npz"))
+
+
+def test_reference_held_calibration_fixture(golden_r2):
+    """Maps + remap on the numbers the reference itself holds (calibration_tests/calibrate_v5: negative focal length
+    in rect_P1, 5-coefficient distortion) — cv2 hashes made by make_golden_r2.py."""
+    meta, _ = golden_r2
+    m = meta["ref_v5"]
+    fx = {k: np.array(v) for k, v in m["fixture"].items()}
+    assert fx["P1"][0, 0] < 0                       # the fixture's own oddity: negative focal length
+    W, H = m["size"]
+    q = lambda a: np.rint(a * np.float32(32)).astype(np.int32)
+    src = cases.ref_v5_frame()
+    for cam in (1, 2):
+        for tag, P in (("", fx[f"P{cam}"]), ("_K", fx[f"K{cam}"])):
+            mx, my = oracle.init_undistort_rectify_map(fx[f"K{cam}"], fx[f"d{cam}"], fx[f"R{cam}"], P, (W, H))
+            assert [_sha(q(mx)), _sha(q(my))] == m[f"mapq{tag}_{cam}"], (cam, tag)
+            assert _sha(oracle.remap(src, mx, my)) == m[f"remap{tag}_{cam}"], (cam, tag)
+
+
+def test_chain_c2_pipeline(golden_r2):
+    """Raw 1280x720 BGR pair -> remap x2 -> BGR2GRAY x2 -> SGBM -> reprojectImageTo3D -> box medians, link by link
+    against cv2 (hashes), XYZ within 1e-5 relative."""
+    meta, npz = golden_r2
+    c = meta["chain_c2"]
+    W, H = 1280, 720
+    L, R = cases.chain_c2_inputs()
+    assert [_sha(L), _sha(R)] == c["in_sha"]
+    K1, d1, K2, d2, _, _ = synth.synthetic_rig(W, H)
+    rc = {k: np.array(v) for k, v in c["rectify"].items()}
+    m1 = oracle.init_undistort_rectify_map(K1, d1, rc["R1"], rc["P1"], (W, H))
+    m2 = oracle.init_undistort_rectify_map(K2, d2, rc["R2"], rc["P2"], (W, H))
+    Lr, Rr = oracle.remap(L, *m1), oracle.remap(R, *m2)
+    assert [_sha(Lr), _sha(Rr)] == c["rect"]
+    Lg, Rg = oracle.bgr2gray(Lr), oracle.bgr2gray(Rr)
+    assert [_sha(Lg), _sha(Rg)] == c["gray"]
+    disp = oracle.sgbm_compute(Lg, Rg, **c["kw"])
+    assert _sha(disp) == c["disp"]
+    xyz = oracle.reproject_to_3d(disp.astype(np.float32) / 16, rc["Q"])[::8, ::8]
+    ref = npz["chain_c2_xyz"]
+    fin = np.isfinite(ref)
+    assert np.array_equal(np.isfinite(xyz), fin)
+    assert (np.abs(xyz[fin] - ref[fin]) / np.maximum(np.abs(ref[fin]), 1e-30)).max() <= 1e-5
+    med = oracle.box_median_depth(disp, rc["Q"], npz["chain_c2_boxes"], -16)
+    refm = npz["chain_c2_med"]
+    assert np.array_equal(np.isnan(med), np.isnan(refm))
+    ok = ~np.isnan(refm)
+    assert (np.abs(med[ok] - refm[ok]) / np.abs(refm[ok])).max() <= 1e-5
