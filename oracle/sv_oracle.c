@@ -761,8 +761,28 @@ void svo_undistort_points(const double *src, int n, const double *K, const doubl
             for (int c = 0; c < 3; c++) t[3 * r + c] = P33[3 * r] * RR[c] + P33[3 * r + 1] * RR[3 + c] + P33[3 * r + 2] * RR[6 + c];
         memcpy(RR, t, sizeof RR);
     }
+    double imt[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1};
+    const int has_tilt = k[12] != 0.0 || k[13] != 0.0;
+    if (has_tilt) {   /* inverse tilt projection = matRotXY^T * invProjZ */
+        const double ctx_ = cos(k[12]), stx = sin(k[12]), cty = cos(k[13]), sty = sin(k[13]);
+        const double rot[9] = {cty, sty * stx, -sty * ctx_, 0, ctx_, stx, sty, -cty * stx, cty * ctx_};
+        const double inv = 1. / rot[8];
+        const double ipz[9] = {inv, 0, inv * rot[2], 0, inv, inv * rot[5], 0, 0, 1};
+        for (int i = 0; i < 3; i++)
+            for (int j = 0; j < 3; j++) {
+                double s = 0;
+                for (int t = 0; t < 3; t++) s += rot[t * 3 + i] * ipz[t * 3 + j];
+                imt[i * 3 + j] = s;
+            }
+    }
     for (int i = 0; i < n; i++) {
         double x = (src[2 * i] - cx) / fx, y = (src[2 * i + 1] - cy) / fy;
+        if (has_tilt) {
+            const double vx = imt[0] * x + imt[1] * y + imt[2], vy = imt[3] * x + imt[4] * y + imt[5];
+            const double vz = imt[6] * x + imt[7] * y + imt[8];
+            const double ip = vz != 0.0 ? 1. / vz : 1.;
+            x = ip * vx; y = ip * vy;
+        }
         const double x0 = x, y0 = y;
         for (int it = 0; it < 5; it++) {
             const double r2 = x * x + y * y;

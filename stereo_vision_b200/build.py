@@ -16,7 +16,7 @@ CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(HERE, "_obj")
 SO = os.path.join(HERE, "libsvb.so")
 SOURCES = ["svb_api.cu", "svb_rectify.cu", "svb_cost.cu", "svb_aggregate.cu", "svb_post.cu", "svb_depth.cu", "svb_bench.cu", "svb_sparse.cu"]
-AGG_PARTS = 5
+AGG_PARTS = 7
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC",
          "-Xcompiler", "-fvisibility=default", "--threads", "2"]

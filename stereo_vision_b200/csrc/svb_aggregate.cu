@@ -31,6 +31,7 @@
 //     lane-parallel every 24 pixels (flush).
 #include "svb_common.cuh"
 #include <stdlib.h>
+#include <algorithm>
 
 #ifndef AGG_MIN3
 #define AGG_MIN3 1         // dir_update: one VIMNMX3 per register (0: VIMNMX + VIADDMNMX)
@@ -82,6 +83,7 @@ struct AggArgs {
     uint32_t one;          // == 1 (an opaque multiplier: x * one + y stays an IMAD on the FMA pipe)
     uint32_t k16;          // == 65536, likewise (x * k16 + y instead of a PRMT / shift on the ALU pipe)
     int uniq, invalid16;
+    int tw;                // MODE_SGBM_3WAY selection rules (winner among equal minima, integer uniqueness threshold)
     int pubmask;           // publish progress when (pixels done & pubmask) < AGG_PPS
     int slack;             // extra producer lead a starving band waits for (0 when one frame is in flight)
 };
@@ -300,7 +302,8 @@ __device__ __forceinline__ void select_flush(const AggArgs &a, int16_t *dpre, un
 {
     const int minS = (int)(best >> 16), bestD = (int)(best & 0xFFFFu);
     bool fail = minS >= 32767;   // all costs saturated: cv2 ends with bestDisp=-1 -> INVALID
-    if (a.uniq > 0) fail = fail || ((int)s2 * (100 - a.uniq) < minS * 100);
+    if (a.uniq > 0)   // cv2's 3-way mode compares against a precomputed integer threshold (oracle: select_impl)
+        fail = fail || (a.tw ? (int)s2 <= (minS * 100) / (100 - a.uniq) : (int)s2 * (100 - a.uniq) < minS * 100);
     int out = a.invalid16;
     if (!fail) {
         const int x2 = x_full - bestD - a.minD;
@@ -333,11 +336,14 @@ struct SweepSmem {
 };
 
 // Per-thread state of a compute lane.  All arrays are indexed by compile-time constants only.
-template <int NR, int G, int NGRP, int NV, bool PASS2, bool SAFE, bool PAD, int PFD>
+// PASS2: add pass-1 S and select the disparity (else: store S).  REV: walk the image rotated by 180 degrees (the four
+// "reverse" path directions).  REV without PASS2 is the latency form of pass 2: it runs concurrently with pass 1 and
+// leaves its own four-path sum in a second volume (k_select_sum finishes the job).
+template <int NR, int G, int NGRP, int NV, bool PASS2, bool SAFE, bool PAD, int PFD, bool REV = PASS2>
 struct SweepLane {
     static constexpr int E = 2 * NR;
     static constexpr int DP = G * E;                // padded disparities of this instantiation (== a.Dp)
-    static constexpr int XDIR = PASS2 ? -1 : 1;     // pass 2 walks every row right to left (and the rows bottom-up)
+    static constexpr int XDIR = REV ? -1 : 1;       // reverse sweeps walk every row right to left (and the rows bottom-up)
     // pass 2: selection one pixel-time behind the path updates (not for the single-path kernel: nothing to overlap with)
     static constexpr bool SELPIPE = AGG_SELPIPE && NV > 0;
     // loop-invariant
@@ -468,13 +474,13 @@ struct SweepLane {
             }
             // with SELPIPE the selection of this pixel runs one pixel-time later, interleaved with the next pixel's paths
             st_regs<NR>(scratch + (PH & 1) * DP + lane * E, s);
-            if (!SELPIPE) select<PH>(parkw + PH, a.k16);
+            if (!SELPIPE) select<PH>(parkw + PH, a.k16, a.tw);
         }
     }
 
     // pass 2: winner / second best / subpixel taps of the pixel whose clamped S sits in scratch half PHP & 1
     template <int PHP>
-    __device__ __forceinline__ void select(uint4 *dst, uint32_t k16)
+    __device__ __forceinline__ void select(uint4 *dst, uint32_t k16, int tw = 0)
     {
         const int16_t *sc = scratch + (PHP & 1) * DP;
         __syncwarp();
@@ -488,7 +494,26 @@ struct SweepLane {
             lk = min(lk, s[k] * k16 + (d0 + 2 * k));                   // (S_lo << 16) | d, as an IMAD (FMA pipe)
             lk = min(lk, __byte_perm(s[k], d0 + 2 * k + 1, 0x3254));   // (S_hi << 16) | d
         }
-        const uint32_t best = group_min_u32<G>(lk);
+        uint32_t best = group_min_u32<G>(lk);
+        if (NV == 0 && tw) {
+            // MODE_SGBM_3WAY (cv2's 8-lane SIMD search): in every residue class d mod 8 the LAST d attaining the
+            // minimum is kept, then the smallest of those wins.  This lane's elements are d0 + e, d0 a multiple of 8:
+            // residue j lives in elements j and j + 8 of every lane.
+            const uint32_t minS = best >> 16;
+            uint32_t bd = 0xFFFFu;
+#pragma unroll
+            for (int j = 0; j < 8; j++) {
+                uint32_t last = 0;                                   // (d + 1) of this lane's last match in class j
+#pragma unroll
+                for (int e = j; e < E; e += 8) {
+                    const uint32_t v = (e & 1) ? (s[e >> 1] >> 16) : (s[e >> 1] & 0xFFFFu);
+                    if (v == minS) last = d0 + e + 1;
+                }
+                last = group_max_u32<G>(last);
+                if (last) bd = min(bd, last - 1);
+            }
+            best = (minS << 16) | bd;
+        }
         const int bestD = (int)(best & 0xFFFFu);
         // second-best S outside bestD-1..bestD+1 (mask table indexed by bestD relative to this lane)
         uint32_t s2;
@@ -532,7 +557,7 @@ __device__ __forceinline__ void cta_barrier() { asm volatile("bar.sync 0;" ::: "
 // NV = 3: wavefront sweep with the three vertical/diagonal predecessors (+ one DMA warp per CTA);
 // NV = 1: same machinery, vertical predecessor only (MODE_HH4: 2 + 2 paths);
 // NV = 0: horizontal path only (rows independent; the 5th path of MODE_SGBM), no barriers, no DMA warp.
-template <int NR, int G, int NGRP, int NV, bool PASS2, bool SAFE, bool PAD, int PFD>
+template <int NR, int G, int NGRP, int NV, bool PASS2, bool SAFE, bool PAD, int PFD, bool REV = PASS2>
 __global__ void __launch_bounds__(NGRP *G + (NV ? 32 : 0)) k_sweep(const __grid_constant__ AggArgs a)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -678,16 +703,16 @@ __global__ void __launch_bounds__(NGRP *G + (NV ? 32 : 0)) k_sweep(const __grid_
     }
 
     // ================= compute lanes =================
-    SweepLane<NR, G, NGRP, NV, PASS2, SAFE, PAD, PFD> st;
+    SweepLane<NR, G, NGRP, NV, PASS2, SAFE, PAD, PFD, REV> st;
     const int g = tid / G, lane = tid % G;
     const int v = band * NGRP + g;
-    typedef SweepLane<NR, G, NGRP, NV, PASS2, SAFE, PAD, PFD> Lane;
+    typedef SweepLane<NR, G, NGRP, NV, PASS2, SAFE, PAD, PFD, REV> Lane;
     st.W1 = W1; st.VS = VS; st.lane = lane;
     st.lag = NV ? AGG_LAG * g : 0;
     st.rowActive = v < a.H;
     st.isRow0 = (g == 0);
-    st.y = PASS2 ? a.H - 1 - v : v;          // pass 2 runs on the image rotated by 180 degrees (a.flip == PASS2)
-    st.xbase = PASS2 ? W1 - 1 : 0;
+    st.y = REV ? a.H - 1 - v : v;            // reverse sweeps run on the image rotated by 180 degrees (a.flip == REV)
+    st.xbase = REV ? W1 - 1 : 0;
     st.P1d = a.P1d; st.P2d = a.P2d;
 #pragma unroll
     for (int k = 0; k < NR; k++)
@@ -742,7 +767,7 @@ __global__ void __launch_bounds__(NGRP *G + (NV ? 32 : 0)) k_sweep(const __grid_
 }
 
 // ---------------- host side ----------------
-template <int NR, int G, int NGRP, int NV, bool PASS2, bool SAFE, bool PAD>
+template <int NR, int G, int NGRP, int NV, bool PASS2, bool SAFE, bool PAD, bool REV = PASS2>
 static int launch_sweep_t(const AggArgs &a, int ngrid, cudaStream_t st)
 {
 #ifndef AGG_PFD2
@@ -750,7 +775,7 @@ static int launch_sweep_t(const AggArgs &a, int ngrid, cudaStream_t st)
 #endif
     constexpr int PFD = NR == 4 ? (PASS2 ? AGG_PFD2 : 4) : 2;   // C prefetch depth in pixels (pass 2 is short of registers)
     const size_t smem = SweepSmem<NGRP, NV, PASS2>::bytes(a.Dp, 2 * NR);
-    auto kern = k_sweep<NR, G, NGRP, NV, PASS2, SAFE, PAD, PFD>;
+    auto kern = k_sweep<NR, G, NGRP, NV, PASS2, SAFE, PAD, PFD, REV>;
     // the opt-in is per device and per function; setting it on every launch is cheap and stays correct with several
     // devices / host threads in one process
     SVB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -759,30 +784,30 @@ static int launch_sweep_t(const AggArgs &a, int ngrid, cudaStream_t st)
     return SVB_OK;
 }
 
-template <int NV, bool PASS2, bool SAFE, bool PAD>
+template <int NV, bool PASS2, bool SAFE, bool PAD, bool REV>
 static int launch_sweep_g(int NR, int G, const AggArgs &a, int ngrid, cudaStream_t st)
 {
-    if (NR == 8) return launch_sweep_t<8, 32, 7, NV, PASS2, SAFE, PAD>(a, ngrid, st);
+    if (NR == 8) return launch_sweep_t<8, 32, 7, NV, PASS2, SAFE, PAD, REV>(a, ngrid, st);
     switch (G) {
-    case 2: return launch_sweep_t<4, 2, 16, NV, PASS2, SAFE, PAD>(a, ngrid, st);
-    case 4: return launch_sweep_t<4, 4, 16, NV, PASS2, SAFE, PAD>(a, ngrid, st);
-    case 8: return launch_sweep_t<4, 8, 16, NV, PASS2, SAFE, PAD>(a, ngrid, st);
-    case 16: return launch_sweep_t<4, 16, 16, NV, PASS2, SAFE, PAD>(a, ngrid, st);
-    default: return launch_sweep_t<4, 32, 15, NV, PASS2, SAFE, PAD>(a, ngrid, st);
+    case 2: return launch_sweep_t<4, 2, 16, NV, PASS2, SAFE, PAD, REV>(a, ngrid, st);
+    case 4: return launch_sweep_t<4, 4, 16, NV, PASS2, SAFE, PAD, REV>(a, ngrid, st);
+    case 8: return launch_sweep_t<4, 8, 16, NV, PASS2, SAFE, PAD, REV>(a, ngrid, st);
+    case 16: return launch_sweep_t<4, 16, 16, NV, PASS2, SAFE, PAD, REV>(a, ngrid, st);
+    default: return launch_sweep_t<4, 32, 15, NV, PASS2, SAFE, PAD, REV>(a, ngrid, st);
     }
 }
 
-template <int NV, bool PASS2>
+template <int NV, bool PASS2, bool REV = PASS2>
 static int launch_sweep(int safe, int pad, int NR, int G, const AggArgs &a, int ngrid, cudaStream_t st)
 {
-    if (safe) return pad ? launch_sweep_g<NV, PASS2, true, true>(NR, G, a, ngrid, st)
-                         : launch_sweep_g<NV, PASS2, true, false>(NR, G, a, ngrid, st);
-    return pad ? launch_sweep_g<NV, PASS2, false, true>(NR, G, a, ngrid, st)
-               : launch_sweep_g<NV, PASS2, false, false>(NR, G, a, ngrid, st);
+    if (safe) return pad ? launch_sweep_g<NV, PASS2, true, true, REV>(NR, G, a, ngrid, st)
+                         : launch_sweep_g<NV, PASS2, true, false, REV>(NR, G, a, ngrid, st);
+    return pad ? launch_sweep_g<NV, PASS2, false, true, REV>(NR, G, a, ngrid, st)
+               : launch_sweep_g<NV, PASS2, false, false, REV>(NR, G, a, ngrid, st);
 }
 
-// The five (NV, PASS2) families are compiled as separate translation units (build.py: -DSVB_AGG_PART=0..4) so that
-// the 120 kernel instantiations build in parallel; without the define everything lands in one object.
+// The seven (NV, PASS2, REV) families are compiled as separate translation units (build.py: -DSVB_AGG_PART=0..6) so
+// that the 168 kernel instantiations build in parallel; without the define everything lands in one object.
 #ifndef SVB_AGG_PART
 #define SVB_AGG_PART -1
 #endif
@@ -792,6 +817,19 @@ static int launch_sweep(int safe, int pad, int NR, int G, const AggArgs &a, int 
     {                                                                                                        \
         return launch_sweep<NV, PASS2>(safe, pad, NR, G, a, ngrid, st);                                      \
     }
+#define SVB_SWEEP_DEF_REVSTORE(NAME, NV)                                                                     \
+    int NAME(int safe, int pad, int NR, int G, const AggArgs &a, int ngrid, cudaStream_t st)                 \
+    {                                                                                                        \
+        return launch_sweep<NV, false, true>(safe, pad, NR, G, a, ngrid, st);                                \
+    }
+int svb_sweep_nv3_rs(int safe, int pad, int NR, int G, const AggArgs &a, int ngrid, cudaStream_t st);
+int svb_sweep_nv0_rs(int safe, int pad, int NR, int G, const AggArgs &a, int ngrid, cudaStream_t st);
+#if SVB_AGG_PART == -1 || SVB_AGG_PART == 5
+SVB_SWEEP_DEF_REVSTORE(svb_sweep_nv3_rs, 3)
+#endif
+#if SVB_AGG_PART == -1 || SVB_AGG_PART == 6
+SVB_SWEEP_DEF_REVSTORE(svb_sweep_nv0_rs, 0)
+#endif
 int svb_sweep_nv3_p1(int safe, int pad, int NR, int G, const AggArgs &a, int ngrid, cudaStream_t st);
 int svb_sweep_nv3_p2(int safe, int pad, int NR, int G, const AggArgs &a, int ngrid, cudaStream_t st);
 int svb_sweep_nv1_p1(int safe, int pad, int NR, int G, const AggArgs &a, int ngrid, cudaStream_t st);
@@ -814,32 +852,37 @@ SVB_SWEEP_DEF(svb_sweep_nv0_p2, 0, true)
 #endif
 
 #if SVB_AGG_PART == -1 || SVB_AGG_PART == 4
-int svb_launch_aggregate(svb_context *ctx, const SgbmPlan &pl, char *ws, size_t ws_stride, int B, int passes,
-                         cudaStream_t st)
+// Rows [y0, y1) of the volume are aggregated as an image of their own (every mode but MODE_SGBM_3WAY: the whole image).
+static int launch_aggregate_rows(svb_context *ctx, const SgbmPlan &pl, char *ws, size_t ws_stride, int B, int passes,
+                                 int y0, int y1, cudaStream_t st)
 {
-    // reset schedulers / progress / scatter keys
+    const int hs = y1 - y0, nbands = (hs + pl.NG - 1) / pl.NG;
+    const size_t rowC = (size_t)pl.W1 * pl.Dp * 2;
+    // reset schedulers / progress / scatter keys (of these rows)
     if (passes & 1) {
         SVB_CUDA_CHECK(cudaMemsetAsync(ctx->tickets, 0, 2 * sizeof(unsigned), st));
         // one strided memset per buffer for the whole batch (pitch = per-frame workspace stride)
         SVB_CUDA_CHECK(cudaMemset2DAsync(ws + pl.off_prog, ws_stride, 0, 2 * sizeof(unsigned) * pl.nbands, B, st));
-        SVB_CUDA_CHECK(cudaMemset2DAsync(ws + pl.off_key, ws_stride, 0xFF, sizeof(unsigned) * (size_t)pl.H * pl.W, B, st));
+        SVB_CUDA_CHECK(cudaMemset2DAsync(ws + pl.off_key + sizeof(unsigned) * (size_t)y0 * pl.W, ws_stride, 0xFF,
+                                         sizeof(unsigned) * (size_t)hs * pl.W, B, st));
     }
     AggArgs a;
     memset(&a, 0, sizeof a);
-    a.C = (const int16_t *)(ws + pl.off_C);
-    a.S = (int16_t *)(ws + pl.off_S);
+    a.C = (const int16_t *)(ws + pl.off_C + (size_t)y0 * rowC);
+    a.S = (int16_t *)(ws + pl.off_S + (size_t)y0 * rowC);
     a.edge = (int16_t *)(ws + pl.off_edge);
-    a.dpre = (int16_t *)(ws + pl.off_dpre);
-    a.keys = (unsigned *)(ws + pl.off_key);
+    a.dpre = (int16_t *)(ws + pl.off_dpre) + (size_t)y0 * pl.W;
+    a.keys = (unsigned *)(ws + pl.off_key) + (size_t)y0 * pl.W;
     a.ws_stride = ws_stride;
-    a.H = pl.H; a.W = pl.W; a.W1 = pl.W1; a.D = pl.D; a.Dp = pl.Dp; a.minX1 = pl.minX1; a.minD = pl.p.minDisparity;
-    a.nbands = pl.nbands; a.B = B;
+    a.H = hs; a.W = pl.W; a.W1 = pl.W1; a.D = pl.D; a.Dp = pl.Dp; a.minX1 = pl.minX1; a.minD = pl.p.minDisparity;
+    a.nbands = nbands; a.B = B;
     a.P1d = (uint32_t)pl.p.P1 * 0x10001u;
     a.P2d = (uint32_t)pl.p.P2 * 0x10001u;
     a.one = 1;
     a.k16 = 65536;
     a.uniq = pl.p.uniquenessRatio;
     a.invalid16 = pl.invalid16;
+    a.tw = pl.p.mode == 2;
     a.pubmask = AGG_PUB - 1;
     a.slack = 0;   // (hysteresis for starving bands: measured no better than 0 since the edges are L2-prefetched)
     const int pad = pl.Dp != pl.D;
@@ -849,21 +892,46 @@ int svb_launch_aggregate(svb_context *ctx, const SgbmPlan &pl, char *ws, size_t 
     a.prog = (unsigned *)(ws + pl.off_prog);
     a.ticket = ctx->tickets;
     int rc = SVB_OK;
-    const bool hh4 = pl.p.mode == 3;   // left + up, then right + down
+    const bool two = pl.p.mode == 3 || pl.p.mode == 2;   // MODE_HH4: left + up, then right + down; 3WAY: left + up, then right
     if (passes & 1)
-        rc = hh4 ? svb_sweep_nv1_p1(pl.safe, pad, NR, pl.G, a, pl.nbands * B, st)
-                 : svb_sweep_nv3_p1(pl.safe, pad, NR, pl.G, a, pl.nbands * B, st);
+        rc = two ? svb_sweep_nv1_p1(pl.safe, pad, NR, pl.G, a, nbands * B, st)
+                 : svb_sweep_nv3_p1(pl.safe, pad, NR, pl.G, a, nbands * B, st);
     if (rc || !(passes & 2)) return rc;
     a.flip = 1;
-    if (pl.p.mode == 1 || hh4) {   // MODE_HH: right, down-right, down, down-left + selection; MODE_HH4: right, down
+    if (pl.p.mode == 1 || pl.p.mode == 3) {   // MODE_HH: right, down-right, down, down-left + selection; MODE_HH4: right, down
         a.prog = (unsigned *)(ws + pl.off_prog) + pl.nbands;
         a.ticket = ctx->tickets + 1;
-        rc = hh4 ? svb_sweep_nv1_p2(pl.safe, pad, NR, pl.G, a, pl.nbands * B, st)
-                 : svb_sweep_nv3_p2(pl.safe, pad, NR, pl.G, a, pl.nbands * B, st);
-    } else {                // MODE_SGBM: 5th path (from the right) + selection, rows independent
-        rc = svb_sweep_nv0_p2(pl.safe, pad, NR, pl.G, a, pl.nbands * B, st);
+        rc = pl.p.mode == 3 ? svb_sweep_nv1_p2(pl.safe, pad, NR, pl.G, a, nbands * B, st)
+                            : svb_sweep_nv3_p2(pl.safe, pad, NR, pl.G, a, nbands * B, st);
+    } else {                // MODE_SGBM: 5th path (from the right) + selection, rows independent; 3WAY: its third path
+        rc = svb_sweep_nv0_p2(pl.safe, pad, NR, pl.G, a, nbands * B, st);
     }
     return rc;
+}
+
+int svb_launch_aggregate(svb_context *ctx, const SgbmPlan &pl, char *ws, size_t ws_stride, int B, int passes,
+                         cudaStream_t st)
+{
+    return launch_aggregate_rows(ctx, pl, ws, ws_stride, B, passes, 0, pl.H, st);
+}
+
+// MODE_SGBM_3WAY (oracle: sgbm_3way_raw): four row stripes of ceil(H/4) rows, each started `overlap` rows early with
+// its paths and block sums restarted there; a stripe keeps only its own rows.  The stripes run last to first, so that
+// the rows a stripe computes ahead of its own range are overwritten by their owner afterwards.
+int svb_launch_cost_aggregate_3way(svb_context *ctx, const SgbmPlan &pl, char *ws, size_t ws_stride, int B, cudaStream_t st)
+{
+    const int nstripes = 4, stripe = (pl.H + nstripes - 1) / nstripes;
+    const int overlap = pl.p.blockSize / 2 + 1 + (stripe + 9) / 10;   // ceil(0.1 * stripe)
+    for (int n = nstripes - 1; n >= 0; n--) {
+        const int ys = n == 0 ? 0 : std::max(std::min(n * stripe - overlap, pl.H), 0);
+        const int ye = n == nstripes - 1 ? pl.H : std::min((n + 1) * stripe, pl.H);
+        const int keep0 = n == 0 ? 0 : std::min(n * stripe, pl.H);
+        if (ye <= ys || keep0 >= ye) continue;
+        int rc;
+        if ((rc = svb_launch_cost(pl, ws, ws_stride, B, ys, ye, st))) return rc;
+        if ((rc = launch_aggregate_rows(ctx, pl, ws, ws_stride, B, 3, ys, ye, st))) return rc;
+    }
+    return SVB_OK;
 }
 #endif   // SVB_AGG_PART (host dispatch lives in part 4)
 #endif   // !EXP_HARNESS

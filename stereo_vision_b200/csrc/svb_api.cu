@@ -96,8 +96,7 @@ int svb_make_plan(const svb_sgbm_params *raw, int H, int W, int ch, SgbmPlan *pl
     SVB_REQUIRE(ch == 1 || ch == 3, SVB_ERR_INVALID, "sgbm: images must be CV_8UC1 or CV_8UC3 (channels=%d)", ch);
     SVB_REQUIRE(H > 0 && W > 0, SVB_ERR_INVALID, "sgbm: bad image size %dx%d", W, H);
     SVB_REQUIRE(p.numDisparities > 0, SVB_ERR_INVALID, "sgbm: numDisparities must be positive (got %d)", p.numDisparities);
-    SVB_REQUIRE(p.mode == 0 || p.mode == 1 || p.mode == 3, SVB_ERR_UNSUPPORTED,
-                "sgbm: mode %d not implemented (MODE_SGBM=0, MODE_HH=1 and MODE_HH4=3 only)", p.mode);
+    SVB_REQUIRE(p.mode >= 0 && p.mode <= 3, SVB_ERR_INVALID, "sgbm: unknown mode %d", p.mode);
     pl->H = H; pl->W = W; pl->ch = ch;
     const int minD = p.minDisparity, D = p.numDisparities, maxD = minD + D;
     pl->D = D;
@@ -112,6 +111,11 @@ int svb_make_plan(const svb_sgbm_params *raw, int H, int W, int ch, SgbmPlan *pl
     SVB_REQUIRE(pl->R <= 5, SVB_ERR_UNSUPPORTED, "sgbm: blockSize %d > 11 is outside this engine's contract", p.blockSize);
     SVB_REQUIRE(D <= 512, SVB_ERR_UNSUPPORTED, "sgbm: numDisparities %d > 512 is outside this engine's contract", D);
     SVB_REQUIRE(W <= 65535 && H <= 65535, SVB_ERR_UNSUPPORTED, "sgbm: image larger than 65535 px");
+    if (p.mode == 2) {   // MODE_SGBM_3WAY: 4 row stripes; cv2 behaves differently (not modelled) when they are shorter than their overlap
+        const int stripe = (H + 3) / 4, overlap = p.blockSize / 2 + 1 + (stripe + 9) / 10;
+        SVB_REQUIRE(overlap <= stripe, SVB_ERR_UNSUPPORTED,
+                    "sgbm: MODE_SGBM_3WAY needs row stripes (%d rows) at least as long as their overlap (%d): image too short", stripe, overlap);
+    }
     pl->ftzero = p.preFilterCap;
     pl->invalid16 = (minD - 1) * 16;
     pl->nplanes = 2 * ch;
@@ -214,7 +218,7 @@ static int run_front(svb_context *ctx, const SgbmPlan &pl, const uint8_t *left, 
 {
     int rc;
     if ((rc = svb_launch_planes(pl, left, right, pitch, istride, ws, pl.per_frame_bytes, B, st))) return rc;
-    if ((rc = svb_launch_cost(pl, ws, pl.per_frame_bytes, B, st))) return rc;
+    if ((rc = svb_launch_cost(pl, ws, pl.per_frame_bytes, B, 0, pl.H, st))) return rc;
     return SVB_OK;
 }
 
@@ -241,11 +245,17 @@ extern "C" int svb_sgbm_compute(svb_context *ctx, const svb_sgbm_params *raw, co
     SVB_MARK(0);
     if ((rc = svb_launch_planes(pl, left, right, pitch_bytes, image_stride_bytes, ws, pl.per_frame_bytes, B, st))) return rc;
     SVB_MARK(1);
-    if ((rc = svb_launch_cost(pl, ws, pl.per_frame_bytes, B, st))) return rc;
-    SVB_MARK(2);
-    if ((rc = svb_launch_aggregate(ctx, pl, ws, pl.per_frame_bytes, B, 1, st))) return rc;
-    SVB_MARK(3);
-    if ((rc = svb_launch_aggregate(ctx, pl, ws, pl.per_frame_bytes, B, 2, st))) return rc;
+    if (pl.p.mode == 2) {   // stripes: cost + both sweeps per stripe (the stage times report them all under pass 2)
+        SVB_MARK(2);
+        SVB_MARK(3);
+        if ((rc = svb_launch_cost_aggregate_3way(ctx, pl, ws, pl.per_frame_bytes, B, st))) return rc;
+    } else {
+        if ((rc = svb_launch_cost(pl, ws, pl.per_frame_bytes, B, 0, pl.H, st))) return rc;
+        SVB_MARK(2);
+        if ((rc = svb_launch_aggregate(ctx, pl, ws, pl.per_frame_bytes, B, 1, st))) return rc;
+        SVB_MARK(3);
+        if ((rc = svb_launch_aggregate(ctx, pl, ws, pl.per_frame_bytes, B, 2, st))) return rc;
+    }
     SVB_MARK(4);
     if ((rc = svb_launch_lrcheck(pl, ws, pl.per_frame_bytes, B, st))) return rc;
     if ((rc = svb_launch_median3((const int16_t *)(ws + pl.off_dtmp), disp, H, W, W, pl.per_frame_bytes / 2,

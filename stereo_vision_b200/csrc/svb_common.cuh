@@ -82,10 +82,12 @@ static inline size_t svb_align_up(size_t v, size_t a) { return (v + a - 1) / a *
 // kernels' host launchers (defined in the .cu files)
 int svb_launch_planes(const SgbmPlan &pl, const uint8_t *left, const uint8_t *right, size_t pitch, size_t istride,
                       char *ws, size_t ws_stride, int B, cudaStream_t st);
-int svb_launch_cost(const SgbmPlan &pl, char *ws, size_t ws_stride, int B, cudaStream_t st);
+int svb_launch_cost(const SgbmPlan &pl, char *ws, size_t ws_stride, int B, int y0, int y1, cudaStream_t st);
 // passes: bit 0 = pass 1 (4 forward paths), bit 1 = pass 2 (remaining paths + selection)
 int svb_launch_aggregate(svb_context *ctx, const SgbmPlan &pl, char *ws, size_t ws_stride, int B, int passes,
                          cudaStream_t st);
+// MODE_SGBM_3WAY: cost volume + aggregation + selection, stripe by stripe
+int svb_launch_cost_aggregate_3way(svb_context *ctx, const SgbmPlan &pl, char *ws, size_t ws_stride, int B, cudaStream_t st);
 int svb_launch_lrcheck(const SgbmPlan &pl, char *ws, size_t ws_stride, int B, cudaStream_t st);
 int svb_launch_median3(const int16_t *src, int16_t *dst, int H, int W, size_t spitch, size_t sstride, size_t dpitch,
                        size_t dstride, int B, cudaStream_t st);

@@ -231,7 +231,7 @@ __device__ __forceinline__ void pix_cell(const CostWindow<NPL> &cw, const uint4 
 
 struct CostArgs {
     const uint2 *LP; const int16_t *RP; int16_t *Cv;
-    int H, W1, Wr, Dp, D, G, jb0, NW, NPART, CPT, NCB, rows_per_seg, zrow;
+    int H, W1, Wr, Dp, D, G, jb0, NW, NPART, CPT, NCB, rows_per_seg, zrow, y0, y1;
     uint32_t cpad;
     uint32_t one, mone;      // == 1, == 0xFFFFFFFF (opaque multipliers: x * one + y stays an IMAD on the FMA pipe)
     size_t ws_stride;
@@ -352,6 +352,7 @@ __device__ __forceinline__ void cp_async8(uint32_t saddr, const void *gmem)
 
 struct CostTile {   // per-CTA geometry shared by both roles
     int G, Dp, NW, TX, W1, H, PS, T0, ya, yb, r0, r1, NCOL;
+    int ylo;            // input rows are clamped to [ylo, H-1] (0 except for the row stripes of MODE_SGBM_3WAY)
     uint32_t smem0, pix_bytes, left0, left_bytes;   // left0: staged left operands [2][NCH][NCOL] uint2
 };
 
@@ -406,7 +407,7 @@ struct CostProducer {
         arr_bytes = (uint32_t)a.Wr * 16u;                                 // one array of one plane: Wr windows
         rrow_bytes = (size_t)NPL * 3 * arr_bytes;
         rb0 = RP + (size_t)wld * 16;
-        const int rc0 = max(0, min(t.H - 1, t.r0));
+        const int rc0 = max(t.ylo, min(t.H - 1, t.r0));
         stage(t, rc0, 0);
         if (work) load_window<2>(cur, rb0 + (size_t)rc0 * rrow_bytes, arr_bytes);
         asm volatile("cp.async.wait_group 0;" ::: "memory");             // made visible by the caller's __syncthreads
@@ -415,7 +416,7 @@ struct CostProducer {
     __device__ __forceinline__ void row(const CostTile &t, int r, int buf)
     {
         const int it = r - t.r0;
-        if (r < t.r1) stage(t, max(0, min(t.H - 1, r + 1)), (it + 1) & 1);   // next row's left operands
+        if (r < t.r1) stage(t, max(t.ylo, min(t.H - 1, r + 1)), (it + 1) & 1);   // next row's left operands
         const uint32_t sts = sts0 + (uint32_t)buf * t.pix_bytes;
         const uint32_t lds = lds0 + (uint32_t)(it & 1) * t.left_bytes;
 #pragma unroll 1
@@ -441,7 +442,7 @@ struct CostProducer {
                 }
             }
             if (work && (!last || r < t.r1)) {                            // next chunk's window
-                const int rn = max(0, min(t.H - 1, last ? r + 1 : r)), chn = last ? 0 : ch + 1;
+                const int rn = max(t.ylo, min(t.H - 1, last ? r + 1 : r)), chn = last ? 0 : ch + 1;
                 load_window<2>(cur, rb0 + (size_t)rn * rrow_bytes + (size_t)(chn * 6) * arr_bytes, arr_bytes);
             }
         }
@@ -560,7 +561,8 @@ __global__ void __launch_bounds__(COST_ROLE, 1) k_cost_fused(const __grid_consta
     t.left_bytes = (uint32_t)((NPL / 2) * t.NCOL) * 8u;
     t.left0 = t.smem0 + 2u * t.pix_bytes + (uint32_t)(BS * t.TX * t.Dp) * 2u;
     t.T0 = blockIdx.x * t.TX - 8 * (t.G - 1);                              // x of output column 0 of group 0
-    t.ya = blockIdx.y * a.rows_per_seg; t.yb = min(t.ya + a.rows_per_seg, t.H);
+    t.ylo = a.y0;                                                           // rows [y0, y1) of the volume are produced
+    t.ya = a.y0 + blockIdx.y * a.rows_per_seg; t.yb = min(t.ya + a.rows_per_seg, a.y1);
     t.r0 = t.ya - R; t.r1 = t.yb - 1 + R;
     const int b = blockIdx.z;
     const int nring = BS * t.TX * t.Dp / 8;   // ring starts at zero: "subtract the row that leaves the window" is unconditional
@@ -604,7 +606,7 @@ static void cost_jobs(int G, int NCB, uint16_t *job)
         for (int l = 0; l < G && n < COST_ROLE; l++) job[n++] = (uint16_t)((cb << 8) | l);
 #endif
 }
-static CostGeom cost_geom(const SgbmPlan &pl)
+static CostGeom cost_geom(const SgbmPlan &pl, int nrows)
 {
     CostGeom g;
     const int Gc = pl.Dp / 8, BS = 2 * pl.R + 1;
@@ -624,15 +626,16 @@ static CostGeom cost_geom(const SgbmPlan &pl)
     g.NW = NW; g.TX = NW - 2 * pl.R;
     g.NCB = (g.TX + COST_CPB_MAX - 1) / COST_CPB_MAX;
     g.ntiles = (pl.W1 + 8 * (Gc - 1) + g.TX - 1) / g.TX;
-    g.nseg = std::max(1, std::min(8, pl.H / 32));
-    g.rows_per_seg = (pl.H + g.nseg - 1) / g.nseg;
-    g.nseg = (pl.H + g.rows_per_seg - 1) / g.rows_per_seg;
+    g.nseg = std::max(1, std::min(8, nrows / 32));
+    g.rows_per_seg = (nrows + g.nseg - 1) / g.nseg;
+    g.nseg = (nrows + g.rows_per_seg - 1) / g.rows_per_seg;
     g.smem = bytes(NW);
     return g;
 }
 
 template <int NPL, int R, int GT>
-static int launch_cost_fused(const SgbmPlan &pl, const CostGeom &g, char *ws, size_t ws_stride, int B, cudaStream_t st)
+static int launch_cost_fused(const SgbmPlan &pl, const CostGeom &g, char *ws, size_t ws_stride, int B, int y0, int y1,
+                             cudaStream_t st)
 {
     auto kern = k_cost_fused<NPL, R, GT>;
     SVB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g.smem));
@@ -642,6 +645,7 @@ static int launch_cost_fused(const SgbmPlan &pl, const CostGeom &g, char *ws, si
     a.jb0 = pl.W - 1 - pl.minX1 + pl.p.minDisparity;
     a.NW = g.NW; a.NPART = g.NPART; a.CPT = g.CPT; a.NCB = g.NCB; a.rows_per_seg = g.rows_per_seg;
     a.zrow = pl.p.mode == 3 ? pl.H - pl.R : pl.H;
+    a.y0 = y0; a.y1 = y1;
     a.cpad = (uint32_t)(32767 - pl.p.P2) * 0x10001u;
     a.one = 1u; a.mone = 0xFFFFFFFFu;
     a.ws_stride = ws_stride;
@@ -653,24 +657,26 @@ static int launch_cost_fused(const SgbmPlan &pl, const CostGeom &g, char *ws, si
 }
 
 template <int NPL, int GT>
-static int launch_cost_r(const SgbmPlan &pl, const CostGeom &g, char *ws, size_t ws_stride, int B, cudaStream_t st)
+static int launch_cost_r(const SgbmPlan &pl, const CostGeom &g, char *ws, size_t ws_stride, int B, int y0, int y1,
+                         cudaStream_t st)
 {
     switch (pl.R) {
-    case 0: return launch_cost_fused<NPL, 0, GT>(pl, g, ws, ws_stride, B, st);
-    case 1: return launch_cost_fused<NPL, 1, GT>(pl, g, ws, ws_stride, B, st);
-    case 2: return launch_cost_fused<NPL, 2, GT>(pl, g, ws, ws_stride, B, st);
-    case 3: return launch_cost_fused<NPL, 3, GT>(pl, g, ws, ws_stride, B, st);
-    case 4: return launch_cost_fused<NPL, 4, GT>(pl, g, ws, ws_stride, B, st);
-    default: return launch_cost_fused<NPL, 5, GT>(pl, g, ws, ws_stride, B, st);
+    case 0: return launch_cost_fused<NPL, 0, GT>(pl, g, ws, ws_stride, B, y0, y1, st);
+    case 1: return launch_cost_fused<NPL, 1, GT>(pl, g, ws, ws_stride, B, y0, y1, st);
+    case 2: return launch_cost_fused<NPL, 2, GT>(pl, g, ws, ws_stride, B, y0, y1, st);
+    case 3: return launch_cost_fused<NPL, 3, GT>(pl, g, ws, ws_stride, B, y0, y1, st);
+    case 4: return launch_cost_fused<NPL, 4, GT>(pl, g, ws, ws_stride, B, y0, y1, st);
+    default: return launch_cost_fused<NPL, 5, GT>(pl, g, ws, ws_stride, B, y0, y1, st);
     }
 }
 
-int svb_launch_cost(const SgbmPlan &pl, char *ws, size_t ws_stride, int B, cudaStream_t st)
+// rows [y0, y1) of C; input rows are clamped to [y0, H-1] (the whole image: y0 = 0, y1 = H)
+int svb_launch_cost(const SgbmPlan &pl, char *ws, size_t ws_stride, int B, int y0, int y1, cudaStream_t st)
 {
-    const CostGeom g = cost_geom(pl);
+    const CostGeom g = cost_geom(pl, y1 - y0);
     SVB_REQUIRE(g.smem <= 227 * 1024 && g.NW > 2 * pl.R + 1, SVB_ERR_UNSUPPORTED,
                 "sgbm: cost tile does not fit shared memory (%zu bytes)", g.smem);
     const bool g32 = pl.Dp == 256 && g.CPT == 8;   // the 129..256-disparity case gets compile-time strides
-    if (pl.nplanes == 2) return g32 ? launch_cost_r<2, 32>(pl, g, ws, ws_stride, B, st) : launch_cost_r<2, 0>(pl, g, ws, ws_stride, B, st);
-    return g32 ? launch_cost_r<6, 32>(pl, g, ws, ws_stride, B, st) : launch_cost_r<6, 0>(pl, g, ws, ws_stride, B, st);
+    if (pl.nplanes == 2) return g32 ? launch_cost_r<2, 32>(pl, g, ws, ws_stride, B, y0, y1, st) : launch_cost_r<2, 0>(pl, g, ws, ws_stride, B, y0, y1, st);
+    return g32 ? launch_cost_r<6, 32>(pl, g, ws, ws_stride, B, y0, y1, st) : launch_cost_r<6, 0>(pl, g, ws, ws_stride, B, y0, y1, st);
 }

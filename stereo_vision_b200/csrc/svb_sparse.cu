@@ -11,6 +11,8 @@
 
 struct UndistortArgs {
     double k[14];
+    double imt[9];  // inverse tilt (Scheimpflug) projection, identity when k[12] = k[13] = 0
+    int has_tilt;
     double fx, fy, cx, cy;
     double RR[9];   // P[:, :3] * R
 };
@@ -21,6 +23,12 @@ __global__ void k_undistort_points(const T *__restrict__ src, T *__restrict__ ds
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     double x = ((double)src[2 * i] - a.cx) / a.fx, y = ((double)src[2 * i + 1] - a.cy) / a.fy;
+    if (a.has_tilt) {   // compensate the tilt first, as cv2 does
+        const double vx = a.imt[0] * x + a.imt[1] * y + a.imt[2], vy = a.imt[3] * x + a.imt[4] * y + a.imt[5];
+        const double vz = a.imt[6] * x + a.imt[7] * y + a.imt[8];
+        const double ip = vz != 0.0 ? 1. / vz : 1.;
+        x = ip * vx; y = ip * vy;
+    }
     const double x0 = x, y0 = y;
     const double *k = a.k;
 #pragma unroll 1
@@ -130,12 +138,24 @@ extern "C" int svb_undistort_points(svb_context *ctx, const void *src, void *dst
     SVB_REQUIRE(n >= 0, SVB_ERR_INVALID, "undistort_points: negative point count");
     SVB_REQUIRE(ndist == 0 || ndist == 4 || ndist == 5 || ndist == 8 || ndist == 12 || ndist == 14, SVB_ERR_INVALID,
                 "undistort_points: distCoeffs must have 4, 5, 8, 12 or 14 elements (got %d)", ndist);
-    SVB_REQUIRE(ndist < 14 || (dist[12] == 0 && dist[13] == 0), SVB_ERR_UNSUPPORTED, "undistort_points: tilt coefficients not implemented");
     if (n == 0) return SVB_OK;
     UndistortArgs a;
     memset(&a, 0, sizeof a);
     for (int i = 0; i < ndist && i < 14; i++) a.k[i] = dist[i];
     a.fx = K[0]; a.fy = K[4]; a.cx = K[2]; a.cy = K[5];
+    a.has_tilt = a.k[12] != 0.0 || a.k[13] != 0.0;
+    if (a.has_tilt) {   // inverse of the tilt projection: matRotXY^T * invProjZ (same construction as the map kernel's)
+        const double ctx_ = cos(a.k[12]), stx = sin(a.k[12]), cty = cos(a.k[13]), sty = sin(a.k[13]);
+        const double rot[9] = {cty, sty * stx, -sty * ctx_, 0, ctx_, stx, sty, -cty * stx, cty * ctx_};
+        const double inv = 1. / rot[8];
+        const double ipz[9] = {inv, 0, inv * rot[2], 0, inv, inv * rot[5], 0, 0, 1};
+        for (int i = 0; i < 3; i++)
+            for (int j = 0; j < 3; j++) {
+                double s = 0;
+                for (int t = 0; t < 3; t++) s += rot[t * 3 + i] * ipz[t * 3 + j];
+                a.imt[i * 3 + j] = s;
+            }
+    }
     double RR[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1};
     if (R) memcpy(RR, R, sizeof RR);
     if (P33) {

@@ -152,3 +152,65 @@ def test_box_median_depth(sv):
     assert gb.is_cuda
     r1 = oracle.box_median_depth(disp[::-1].copy(), Q, boxes[:4], -16)
     assert np.array_equal(gb.cpu().numpy(), np.where(bi == 0, ref[:4], r1), equal_nan=True)
+
+
+def test_reference_held_calibration_fixture_maps_and_remap(sv):
+    """The only numeric fixture the reference holds for this path (calibration_tests/calibrate_v5: negative focal length
+    in rect_P1 -> maps far outside the image; 5-coefficient distortion): x32-quantised map hashes and remapped frame
+    hashes made by cv2 (tests/golden/make_golden_r2.py)."""
+    import hashlib
+    import json
+    import os
+    import cases
+    sha = lambda a: hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+    with open(os.path.join(os.path.dirname(__file__), "golden", "golden_r2.json")) as f:
+        m = json.load(f)["ref_v5"]
+    fx = {k: np.array(v) for k, v in m["fixture"].items()}
+    W, H = m["size"]
+    q = lambda a: np.rint(a * np.float32(32)).astype(np.int32)
+    src = cases.ref_v5_frame()
+    for cam in (1, 2):
+        for tag, P in (("", fx[f"P{cam}"]), ("_K", fx[f"K{cam}"])):
+            mx, my = sv.initUndistortRectifyMap(fx[f"K{cam}"], fx[f"d{cam}"], fx[f"R{cam}"], P, (W, H), sv.CV_32FC1)
+            assert [sha(q(mx)), sha(q(my))] == m[f"mapq{tag}_{cam}"], (cam, tag)
+            assert sha(sv.remap(src, mx, my, sv.INTER_LINEAR)) == m[f"remap{tag}_{cam}"], (cam, tag)
+
+
+def test_chain_c2_pipeline_matches_cv2_link_by_link(sv):
+    """c2 end to end on the device: raw 1280x720 BGR -> remap x2 -> BGR2GRAY x2 -> StereoSGBM.compute ->
+    reprojectImageTo3D -> box medians; rectified / gray images and disparity by cv2 hash, XYZ and medians <= 1e-5."""
+    import hashlib
+    import json
+    import os
+    import torch
+    import cases
+    sha = lambda a: hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+    gd = os.path.join(os.path.dirname(__file__), "golden")
+    with open(os.path.join(gd, "golden_r2.json")) as f:
+        c = json.load(f)["chain_c2"]
+    npz = np.load(os.path.join(gd, "golden_r2.npz"))
+    W, H = 1280, 720
+    L, R = cases.chain_c2_inputs()
+    assert [sha(L), sha(R)] == c["in_sha"]
+    K1, d1, K2, d2, _, _ = synth.synthetic_rig(W, H)
+    rc = {k: np.array(v) for k, v in c["rectify"].items()}
+    dev = "cuda:0"
+    m1 = sv.initUndistortRectifyMap(K1, d1, rc["R1"], rc["P1"], (W, H), sv.CV_32FC1, device=dev)
+    m2 = sv.initUndistortRectifyMap(K2, d2, rc["R2"], rc["P2"], (W, H), sv.CV_32FC1, device=dev)
+    Ld, Rd = torch.from_numpy(L).to(dev), torch.from_numpy(R).to(dev)
+    Lr, Rr = sv.remap(Ld, *m1, sv.INTER_LINEAR), sv.remap(Rd, *m2, sv.INTER_LINEAR)      # everything stays on the device
+    assert [sha(Lr.cpu().numpy()), sha(Rr.cpu().numpy())] == c["rect"]
+    Lg, Rg = sv.cvtColor(Lr, sv.COLOR_BGR2GRAY), sv.cvtColor(Rr, sv.COLOR_BGR2GRAY)
+    assert [sha(Lg.cpu().numpy()), sha(Rg.cpu().numpy())] == c["gray"]
+    disp = sv.StereoSGBM_create(**c["kw"]).compute(Lg, Rg)
+    assert sha(disp.cpu().numpy()) == c["disp"]
+    xyz = sv.reprojectImageTo3D(disp.to(torch.float32) / 16, rc["Q"]).cpu().numpy()[::8, ::8]
+    ref = npz["chain_c2_xyz"]
+    fin = np.isfinite(ref)
+    assert np.array_equal(np.isfinite(xyz), fin)
+    assert (np.abs(xyz[fin] - ref[fin]) / np.maximum(np.abs(ref[fin]), 1e-30)).max() <= 1e-5
+    med = sv.box_median_depth(disp, rc["Q"], npz["chain_c2_boxes"]).cpu().numpy()
+    refm = npz["chain_c2_med"]
+    assert np.array_equal(np.isnan(med), np.isnan(refm))
+    ok = ~np.isnan(refm)
+    assert (np.abs(med[ok] - refm[ok]) / np.abs(refm[ok])).max() <= 1e-5

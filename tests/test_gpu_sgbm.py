@@ -99,8 +99,10 @@ def test_error_behaviour(sv):
         m.compute(z.astype(np.float32), z.astype(np.float32))
     with pytest.raises(ValueError):
         m.compute(z[:, :60], z[:, :60])          # too narrow (cv2.error -2)
-    with pytest.raises(NotImplementedError):
-        sv.StereoSGBM_create(numDisparities=16, mode=2).compute(z, z)
+    with pytest.raises(NotImplementedError):       # MODE_SGBM_3WAY on an image shorter than its stripe overlap
+        sv.StereoSGBM_create(numDisparities=16, blockSize=9, mode=2).compute(z[:12], z[:12])
+    with pytest.raises(ValueError):
+        sv.StereoSGBM_create(numDisparities=16, mode=7).compute(z, z)
     with pytest.raises(ValueError):
         sv.StereoSGBM_create(numDisparities=0).compute(z, z)
     # non-contiguous views are accepted
@@ -202,3 +204,74 @@ def test_geometry_fuzz_vs_oracle(sv):
             if not np.array_equal(got, ref):
                 bad.append((D, bs, ch, minD, H, W, mode, int((got != ref).sum())))
     assert not bad, bad
+
+
+def test_mode_sgbm_3way_matches_cv2_golden(sv):
+    """MODE_SGBM_3WAY (mode 2): 48 small cases bit-exact vs cv2 golden vectors, c1/c2/c3 at full size vs the cv2 hashes,
+    and a batch (the stripes of all frames run together)."""
+    import json
+    import os
+    import torch
+    gd = os.path.join(os.path.dirname(__file__), "golden")
+    g = np.load(os.path.join(gd, "golden_3way.npz"))
+    bad = []
+    for i, c in enumerate(cases.sgbm_3way_cases()):
+        L, R = cases.sgbm_inputs(c)
+        got = sv.StereoSGBM_create(**c["kw"]).compute(L, R)
+        if not np.array_equal(got, g[f"w3_{i}"]):
+            bad.append((i, c, int((got != g[f"w3_{i}"]).sum())))
+    assert not bad, f"{len(bad)} of 48 MODE_SGBM_3WAY cases differ from cv2 golden: {bad[:3]}"
+    with open(os.path.join(gd, "golden_3way_full.json")) as f:
+        full = json.load(f)
+    for name in ("c1", "c2", "c3"):
+        L, R, kw = cases.full_inputs(name)
+        m = sv.StereoSGBM_create(**dict(kw, mode=sv.STEREO_SGBM_MODE_SGBM_3WAY))
+        got = m.compute(L, R)
+        if _sha(got) != full[f"{name}_3way"]:
+            ref = oracle.sgbm_compute(L, R, **dict(kw, mode=2))
+            raise AssertionError(f"{name} 3way: differs from cv2 golden; vs oracle: {(got != ref).sum()} px differ")
+    Lb = torch.from_numpy(np.stack([L] * 3)).cuda()
+    Rb = torch.from_numpy(np.stack([R] * 3)).cuda()
+    out = m.compute_batch(Lb, Rb).cpu().numpy()
+    assert all(_sha(out[b]) == full["c3_3way"] for b in range(3))
+
+
+@pytest.fixture(scope="module")
+def golden_r2():
+    import json
+    import os
+    gd = os.path.join(os.path.dirname(__file__), "golden")
+    with open(os.path.join(gd, "golden_r2.json")) as f:
+        meta = json.load(f)
+    return meta, np.load(os.path.join(gd, "golden_r2.npz"))
+
+
+def test_c3_three_channel_and_negative_min_disparity_full_size(sv, golden_r2):
+    """BASELINE-size holes of round 1: 3-channel input (6-plane cost path + saturating sweep) and minDisparity = -16."""
+    meta, _ = golden_r2
+    H, W, D = 1080, 1920, 256
+    L3, R3 = synth.stereo_pair(H, W, D, seed=1000, channels=3)
+    c = meta["c3_3ch"]
+    assert [_sha(L3), _sha(R3)] == c["in_sha256"]
+    assert _sha(sv.StereoSGBM_create(**c["kw"]).compute(L3, R3)) == c["sha256"]
+    L, R = synth.stereo_pair(H, W, D, seed=1000)
+    c = meta["c3_minD-16"]
+    assert c["kw"]["minDisparity"] == -16
+    assert _sha(sv.StereoSGBM_create(**c["kw"]).compute(L, R)) == c["sha256"]
+
+
+def test_c3_batch_of_32_distinct_frames_matches_cv2_hashes(sv, golden_r2):
+    """The bench regime: 32 DISTINCT 1080p pairs in one batch (72 bands x 32 frames >> resident CTAs), every output
+    checked against cv2's hash of that frame."""
+    import torch
+    meta, _ = golden_r2
+    c = meta["c3_batch"]
+    s0, s1 = c["seeds"]
+    H, W, D = 1080, 1920, 256
+    pairs = [synth.stereo_pair(H, W, D, seed=s) for s in range(s0, s1)]
+    Lb = torch.from_numpy(np.stack([p[0] for p in pairs])).cuda()
+    Rb = torch.from_numpy(np.stack([p[1] for p in pairs])).cuda()
+    out = sv.StereoSGBM_create(**c["kw"]).compute_batch(Lb, Rb).cpu().numpy()
+    bad = [i for i in range(s1 - s0) if _sha(out[i]) != c["sha256"][i]]
+    assert not bad, f"frames {bad} of the 32-frame batch differ from cv2"
+    sv.release_workspaces()

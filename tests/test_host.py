@@ -67,8 +67,9 @@ def test_geometry_and_contract(lib):
     assert (g["minX1"], g["maxX1"], g["Dp"], g["invalid16"]) == (20, 196, 32, -80)
     with pytest.raises(ValueError):
         sv.StereoSGBM_create(numDisparities=64, blockSize=5).geometry(66)      # too narrow: cv2.error -2
-    with pytest.raises(NotImplementedError):
-        sv.StereoSGBM_create(numDisparities=64, mode=2).geometry(640)
+    assert sv.StereoSGBM_create(numDisparities=64, mode=2).geometry(640)["width1"] == 576   # MODE_SGBM_3WAY is in the contract
+    with pytest.raises(ValueError):
+        sv.StereoSGBM_create(numDisparities=64, mode=9).geometry(640)
     with pytest.raises(NotImplementedError):                                   # int16 cost overflow (cv2 wraps)
         sv.StereoSGBM_create(numDisparities=64, blockSize=11, preFilterCap=63, P2=32 * 3 * 121).geometry(640, 3)
 

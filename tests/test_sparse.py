@@ -99,3 +99,24 @@ def test_gpu_bgr2gray_and_undistort(sv):
     assert m1.dtype == np.int16 and m2.dtype == np.uint16
     assert np.array_equal(m1, G["fix_map1"]) and np.array_equal(m2, G["fix_map2"])
     assert np.array_equal(sv.remap(C["bgr_small"], m1, m2, sv.INTER_LINEAR), G["undist_img"])
+
+
+# ------------------------------------------------------------------ 14-coefficient (tilt) undistortPoints
+def _tilt_case():
+    import make_golden_tilt as mt
+    g = np.load(os.path.join(ROOT, "tests", "golden", "golden_tilt.npz"))
+    return mt, g, mt.points()
+
+
+def test_oracle_undistort_points_with_tilt():
+    mt, g, pts = _tilt_case()
+    assert _close(oracle.undistort_points(pts, mt.K, mt.DIST), g["plain"].reshape(-1, 2)) < 1e-12
+    assert _close(oracle.undistort_points(pts, mt.K, mt.DIST, R=g["R"], P=mt.K), g["rect"].reshape(-1, 2)) < 1e-12
+
+
+@pytest.mark.gpu
+def test_gpu_undistort_points_with_tilt(sv):
+    mt, g, pts = _tilt_case()
+    assert _close(sv.undistortPoints(pts.reshape(-1, 1, 2), mt.K, mt.DIST), g["plain"]) < 1e-12
+    assert _close(sv.undistortPoints(pts.reshape(-1, 1, 2), mt.K, mt.DIST, R=g["R"], P=mt.K), g["rect"]) < 1e-12
+    assert _close(sv.undistortPoints(pts.astype(np.float32).reshape(-1, 1, 2), mt.K, mt.DIST, R=g["R"], P=mt.K), g["f32"]) < RTOL

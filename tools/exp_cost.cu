@@ -52,7 +52,7 @@ int main(int argc, char **argv)
         if (svb_launch_planes(pl, dl, dr, (size_t)W * ch, img, ws, pl.per_frame_bytes, B, 0)) { printf("planes: %s\n", svb_last_error()); return 1; }
         cudaEventRecord(e1); cudaEventSynchronize(e1); cudaEventElapsedTime(&ms, e0, e1); best[0] = fminf(best[0], ms);
         cudaEventRecord(e0);
-        if (svb_launch_cost(pl, ws, pl.per_frame_bytes, B, 0)) { printf("cost: %s\n", svb_last_error()); return 1; }
+        if (svb_launch_cost(pl, ws, pl.per_frame_bytes, B, 0, pl.H, 0)) { printf("cost: %s\n", svb_last_error()); return 1; }
         cudaEventRecord(e1); cudaEventSynchronize(e1); cudaEventElapsedTime(&ms, e0, e1); best[1] = fminf(best[1], ms);
     }
     const size_t vol = (size_t)H * pl.W1 * pl.Dp * 2;
