@@ -77,6 +77,13 @@ int svb_sgbm_compute(svb_context *ctx, const svb_sgbm_params *raw, const uint8_t
                      int H, int W, int channels, size_t pitch_bytes, size_t image_stride_bytes, int B,
                      int16_t *disp, size_t disp_pitch_elems, size_t disp_stride_elems, void *ws, size_t ws_bytes,
                      void *stream);
+/* Small jobs (B * ceil(H/15 or 16) <= 74 bands, modes 0 and 1) run in the LATENCY FORM by default: the forward and the
+ * reverse sweep run side by side on two streams (forked from and joined to `stream` by events inside the call), each
+ * into its own sum volume, and a third kernel adds them and selects the disparity — about half the wavefront time of a
+ * single pair (the drop-in cv2.StereoSGBM_create(...).compute(L, R) call), at the price of one more volume in the
+ * workspace (svb_sgbm_workspace_bytes accounts for it).  Results are identical.  svb_set_latency_form(ctx, 0) makes
+ * every job run the two sweeps back to back (the throughput form larger batches always use); 1 restores the default. */
+int svb_set_latency_form(svb_context *ctx, int enable);
 /* Stage taps for parity tests (single pair): cost volume C and the pass-1 aggregate S (sum of the four
  * forward paths; the final S only ever exists in registers), both int16 [H][width1][Dp]; disp_raw = selection
  * + LR-check output before median/speckle.  Any output may be NULL. */

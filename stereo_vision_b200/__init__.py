@@ -4,7 +4,7 @@ from .api import (  # noqa: F401
     BORDER_CONSTANT, CV_16SC2, CV_32FC1, INTER_LINEAR, STEREO_SGBM_MODE_HH, STEREO_SGBM_MODE_HH4,
     STEREO_SGBM_MODE_SGBM, STEREO_SGBM_MODE_SGBM_3WAY, StereoSGBM, StereoSGBM_create, box_median_depth,
     filterSpeckles, initUndistortRectifyMap, last_stage_ms, medianBlur, packed_alu_peak, release_workspaces, remap,
-    reprojectImageTo3D, set_stage_timing,
+    reprojectImageTo3D, set_latency_form, set_stage_timing,
     COLOR_BGR2GRAY, cvtColor, triangulatePoints, triangulate_stereo, undistort, undistortPoints,
 )
 from ._lib import SvbError  # noqa: F401

@@ -30,7 +30,7 @@ EXPORTS = [
     "svb_filter_speckles_s16", "svb_init_undistort_rectify_map", "svb_remap_u8", "svb_reproject_to_3d",
     "svb_box_median_depth", "svb_set_timing", "svb_sgbm_last_stage_ms", "svb_measure_packed_alu_peak",
     "svb_undistort_points", "svb_triangulate_points", "svb_bgr2gray_u8", "svb_init_undistort_rectify_map_fixed",
-    "svb_remap_u8_fixed", "svb_filter_speckles_s16_noalloc",
+    "svb_remap_u8_fixed", "svb_filter_speckles_s16_noalloc", "svb_set_latency_form",
 ]
 
 _lib = None
@@ -65,6 +65,7 @@ def load():
     lib.svb_reproject_to_3d.argtypes = [vp, vp, i32, i32, i32, vp, i32, vp, i32, vp, vp]
     lib.svb_box_median_depth.argtypes = [vp, vp, i32, i32, sz, vp, i32, vp, vp, i32, vp, vp]
     lib.svb_set_timing.argtypes = [vp, i32]
+    lib.svb_set_latency_form.argtypes = [vp, i32]
     lib.svb_sgbm_last_stage_ms.argtypes = [vp, C.POINTER(C.c_float), i32]
     lib.svb_undistort_points.argtypes = [vp, vp, vp, i32, i32, vp, vp, i32, vp, vp, vp]
     lib.svb_triangulate_points.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, vp, vp]

@@ -363,6 +363,13 @@ def box_median_depth(disp16, Q, boxes, minDisparity=0, box_image=None):
 STAGE_NAMES = ("planes", "cost", "aggregate_pass1", "aggregate_pass2_select", "lrcheck_median", "speckle")
 
 
+def set_latency_form(enable: bool, device=None) -> None:
+    """Small jobs (a single pair, e.g. the drop-in compute(L, R) call) run their two sweeps concurrently by default;
+    False forces the back-to-back form that large batches use (identical results; see include/svb.h)."""
+    dev = torch.cuda.current_device() if device is None else int(device)
+    check(_lib.load().svb_set_latency_form(_lib.context(dev), int(bool(enable))))
+
+
 def set_stage_timing(enable: bool, device=None) -> None:
     """Record CUDA events between the stages of StereoSGBM.compute on this device's context."""
     dev = _device_of() if device is None else int(device)

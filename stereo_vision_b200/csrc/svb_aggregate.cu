@@ -91,7 +91,10 @@ struct AggArgs {
 // Progress poll.  A relaxed (L1-bypassing) load, not ld.acquire: ptxas lowers every gpu-scope acquire/fence to
 // LDG + CCTL.IVALL, i.e. an invalidation of the SM's whole L1 on every poll.  The acquire side of the hand-off is one
 // fence_acquire() each time the known progress ADVANCES (at most once per AGG_PUB pixels, not once per poll), issued
-// before the cp.async.cg reads of the vectors that progress value guards.
+// before the cp.async.cg reads of the vectors that progress value guards — and only when the fetch front actually needs
+// pixels beyond the last acquired value (`acq`): a consumer whose producer is far ahead (the normal case with several
+// frames in flight) fences once per producer lead, not once per publication.  (A fence on every advance cost 2.8 % of
+// both sweeps at B = 32: tools/exp_sweep.cu, 17.07 -> 17.56 / 21.63 -> 22.24 ms.)
 __device__ __forceinline__ unsigned ld_relaxed(const unsigned *p)
 {
     unsigned v;
@@ -644,6 +647,7 @@ __global__ void __launch_bounds__(NGRP *G + (NV ? 32 : 0)) k_sweep(const __grid_
         if (AGG_L2PF > 0 && consumer)
             for (; l2pf < min(AGG_L2PF, W1); l2pf++) l2fetch(l2pf);
         unsigned known = consumer ? 0u : (unsigned)W1, pending = 0;
+        unsigned acq = known;              // progress value the last acquire fence covered: pixels < acq may be fetched
         int fetched = consumer ? 0 : W1;   // pixels [0, fetched) are issued
         int f1 = fetched, f2 = fetched;    // 'fetched' one and two steps ago
 #ifdef EXP_NOPOLL
@@ -655,7 +659,6 @@ __global__ void __launch_bounds__(NGRP *G + (NV ? 32 : 0)) k_sweep(const __grid_
             // in which row 0 reads pixels < t+PPS+1
             const int need = min(t + AGG_PPS + 1, W1);
             if (consumer) {
-                const unsigned known0 = known;
                 known = max(known, pending);
                 if (known < (unsigned)W1) pending = ld_relaxed(prog_in);
 #ifdef EXP_HARNESS
@@ -670,11 +673,14 @@ __global__ void __launch_bounds__(NGRP *G + (NV ? 32 : 0)) k_sweep(const __grid_
                   if (lane == 0) atomicAdd(&g_spin[1], (unsigned long long)(clock64() - c0)); }
                 if (lane == 0) atomicAdd(&g_spin[2], 1ull);
 #endif
-#ifndef AGG_NOFENCE
-                if (known != known0) fence_acquire();   // orders the vector reads below after the flag read
-#endif
                 constexpr int EPF = AGG_EDGE_LIKE_ROW(G) ? AGG_SLOTS - AGG_PPS - 2 : AGG_EPF;
-                const int limit = min(min(t + 1 + EPF, W1), (int)known);
+                const int want = min(t + 1 + EPF, W1);
+#ifndef AGG_NOFENCE
+                if ((int)acq < want && known > acq) { fence_acquire(); acq = known; }   // orders the vector reads below after the flag read
+#else
+                acq = known;
+#endif
+                const int limit = min(want, (int)acq);
 #pragma unroll
                 for (int i = 0; i < 2 * AGG_PPS; i++)
                     if (fetched < limit) fetch(fetched++);
@@ -852,6 +858,88 @@ SVB_SWEEP_DEF(svb_sweep_nv0_p2, 0, true)
 #endif
 
 #if SVB_AGG_PART == -1 || SVB_AGG_PART == 4
+// ---- latency form: S = S1 + S2 (the two concurrent sweeps' sums), then the selection ----
+// A group of G lanes owns one pixel at a time (E disparities per lane, as in k_sweep); a warp works on 32 / G pixels side
+// by side and walks its share of the row.  Same selection rules as SweepLane::select + select_flush.
+struct SelSumArgs {
+    const int16_t *S1, *S2;
+    AggArgs a;   // geometry, uniqueness, dpre / keys (C, S, edge, prog, ticket unused)
+};
+template <int NR, int G>
+__global__ void __launch_bounds__(256) k_select_sum(const __grid_constant__ SelSumArgs q)
+{
+    constexpr int E = 2 * NR, DP = G * E, PPW = 32 / G;             // pixels per warp step
+    __shared__ __align__(16) int16_t sc[8][PPW][DP];                  // per warp: the summed vectors (subpixel taps)
+    const AggArgs &a = q.a;
+    const int y = blockIdx.x, b = blockIdx.y;
+    const int wid = threadIdx.x >> 5, lw = threadIdx.x & 31, sub = lw / G, lane = lw % G;
+    const size_t fo = (size_t)b * a.ws_stride;
+    const int16_t *S1 = reinterpret_cast<const int16_t *>(reinterpret_cast<const char *>(q.S1) + fo) + (size_t)y * a.W1 * DP;
+    const int16_t *S2 = reinterpret_cast<const int16_t *>(reinterpret_cast<const char *>(q.S2) + fo) + (size_t)y * a.W1 * DP;
+    int16_t *dpre = reinterpret_cast<int16_t *>(reinterpret_cast<char *>(a.dpre) + fo);
+    unsigned *keys = reinterpret_cast<unsigned *>(reinterpret_cast<char *>(a.keys) + fo);
+    const uint32_t d0 = (uint32_t)lane * E;
+    uint32_t keep[NR];
+#pragma unroll
+    for (int k = 0; k < NR; k++)
+        keep[k] = ((d0 + 2 * k < (uint32_t)a.D) ? 0x0000FFFFu : 0u) | ((d0 + 2 * k + 1 < (uint32_t)a.D) ? 0xFFFF0000u : 0u);
+    for (int x0 = wid * PPW; x0 < a.W1; x0 += 8 * PPW) {
+        const int x = x0 + sub;
+        const bool act = x < a.W1;
+        uint32_t s[NR], t[NR];
+        ld_regs_stream<NR>(S1 + (size_t)(act ? x : 0) * DP + d0, s);
+        ld_regs_stream<NR>(S2 + (size_t)(act ? x : 0) * DP + d0, t);
+#pragma unroll
+        for (int k = 0; k < NR; k++) {
+            s[k] = __vminu2(s[k] + t[k], 0x7FFF7FFFu);               // both <= 0x7FFF per half: no carry; saturating sum
+            s[k] |= 0x7FFF7FFFu & ~keep[k];                          // padded disparities never win
+        }
+        int16_t *row = sc[wid][sub];
+        __syncwarp();
+        st_regs<NR>(row + d0, s);
+        uint32_t lk = 0xFFFFFFFFu;
+#pragma unroll
+        for (int k = 0; k < NR; k++) {
+            lk = min(lk, (s[k] << 16) | (d0 + 2 * k));
+            lk = min(lk, (s[k] & 0xFFFF0000u) | (d0 + 2 * k + 1));
+        }
+        const uint32_t best = group_min_u32<G>(lk);
+        const int bestD = (int)(best & 0xFFFFu);
+        uint32_t m2 = 0x7FFFu;                                        // second best outside bestD-1 .. bestD+1
+#pragma unroll
+        for (int k = 0; k < NR; k++) {
+            const int da = (int)d0 + 2 * k - bestD, db = da + 1;
+            if (da < -1 || da > 1) m2 = min(m2, s[k] & 0xFFFFu);
+            if (db < -1 || db > 1) m2 = min(m2, s[k] >> 16);
+        }
+        const uint32_t s2 = group_min_u32<G>(m2);
+        __syncwarp();
+        if (lane == 0 && act) {
+            const uint32_t sm1 = (uint16_t)row[max(bestD - 1, 0)], sp1 = (uint16_t)row[min(bestD + 1, DP - 1)];
+            select_flush(a, dpre, keys, y, x + a.minX1, best, s2, sm1 | (sp1 << 16));
+        }
+    }
+}
+
+template <int NR, int G>
+static int launch_select_sum_t(const SelSumArgs &q, int H, int B, cudaStream_t st)
+{
+    k_select_sum<NR, G><<<dim3(H, B), 256, 0, st>>>(q);
+    SVB_CUDA_CHECK(cudaGetLastError());
+    return SVB_OK;
+}
+static int launch_select_sum(int NR, int G, const SelSumArgs &q, int H, int B, cudaStream_t st)
+{
+    if (NR == 8) return launch_select_sum_t<8, 32>(q, H, B, st);
+    switch (G) {
+    case 2: return launch_select_sum_t<4, 2>(q, H, B, st);
+    case 4: return launch_select_sum_t<4, 4>(q, H, B, st);
+    case 8: return launch_select_sum_t<4, 8>(q, H, B, st);
+    case 16: return launch_select_sum_t<4, 16>(q, H, B, st);
+    default: return launch_select_sum_t<4, 32>(q, H, B, st);
+    }
+}
+
 // Rows [y0, y1) of the volume are aggregated as an image of their own (every mode but MODE_SGBM_3WAY: the whole image).
 static int launch_aggregate_rows(svb_context *ctx, const SgbmPlan &pl, char *ws, size_t ws_stride, int B, int passes,
                                  int y0, int y1, cudaStream_t st)
@@ -913,6 +1001,59 @@ int svb_launch_aggregate(svb_context *ctx, const SgbmPlan &pl, char *ws, size_t 
                          cudaStream_t st)
 {
     return launch_aggregate_rows(ctx, pl, ws, ws_stride, B, passes, 0, pl.H, st);
+}
+
+// Latency form (SgbmPlan::latency): the forward sweep on `st`, the reverse sweep on ctx->aux at the same time (own sum
+// volume, own band-edge buffer, own tickets / progress counters), joined by events, then k_select_sum.
+int svb_launch_aggregate_concurrent(svb_context *ctx, const SgbmPlan &pl, char *ws, size_t ws_stride, int B, cudaStream_t st,
+                                    cudaEvent_t mark_pass1)
+{
+    SVB_CUDA_CHECK(cudaMemsetAsync(ctx->tickets, 0, 2 * sizeof(unsigned), st));
+    SVB_CUDA_CHECK(cudaMemset2DAsync(ws + pl.off_prog, ws_stride, 0, 2 * sizeof(unsigned) * pl.nbands, B, st));
+    SVB_CUDA_CHECK(cudaMemset2DAsync(ws + pl.off_key, ws_stride, 0xFF, sizeof(unsigned) * (size_t)pl.H * pl.W, B, st));
+    AggArgs a;
+    memset(&a, 0, sizeof a);
+    a.C = (const int16_t *)(ws + pl.off_C);
+    a.dpre = (int16_t *)(ws + pl.off_dpre);
+    a.keys = (unsigned *)(ws + pl.off_key);
+    a.ws_stride = ws_stride;
+    a.H = pl.H; a.W = pl.W; a.W1 = pl.W1; a.D = pl.D; a.Dp = pl.Dp; a.minX1 = pl.minX1; a.minD = pl.p.minDisparity;
+    a.nbands = pl.nbands; a.B = B;
+    a.P1d = (uint32_t)pl.p.P1 * 0x10001u;
+    a.P2d = (uint32_t)pl.p.P2 * 0x10001u;
+    a.one = 1; a.k16 = 65536;
+    a.uniq = pl.p.uniquenessRatio; a.invalid16 = pl.invalid16; a.tw = 0;
+    a.pubmask = AGG_PUB - 1;   // (publishing every barrier is slower even for one frame: st.release costs more than the
+                               // shorter hand-off gains — tools/exp_sweep.cu, B = 1: 3.54 ms at 8 pixels, 4.53 ms at 2)
+    a.slack = 0;
+    const int pad = pl.Dp != pl.D, NR = pl.E / 2;
+    SVB_CUDA_CHECK(cudaEventRecord(ctx->ev_fork, st));
+    SVB_CUDA_CHECK(cudaStreamWaitEvent(ctx->aux, ctx->ev_fork, 0));
+    // reverse sweep (aux): MODE_HH right, down-right, down, down-left; MODE_SGBM: the single path from the right
+    AggArgs r = a;
+    r.flip = 1;
+    r.S = (int16_t *)(ws + pl.off_S2);
+    r.edge = (int16_t *)(ws + pl.off_edge2);
+    r.prog = (unsigned *)(ws + pl.off_prog) + pl.nbands;
+    r.ticket = ctx->tickets + 1;
+    int rc = pl.p.mode == 1 ? svb_sweep_nv3_rs(pl.safe, pad, NR, pl.G, r, pl.nbands * B, ctx->aux)
+                            : svb_sweep_nv0_rs(pl.safe, pad, NR, pl.G, r, pl.nbands * B, ctx->aux);
+    if (rc) return rc;
+    SVB_CUDA_CHECK(cudaEventRecord(ctx->ev_join, ctx->aux));
+    // forward sweep (st): left, up-left, up, up-right
+    a.flip = 0;
+    a.S = (int16_t *)(ws + pl.off_S);
+    a.edge = (int16_t *)(ws + pl.off_edge);
+    a.prog = (unsigned *)(ws + pl.off_prog);
+    a.ticket = ctx->tickets;
+    if ((rc = svb_sweep_nv3_p1(pl.safe, pad, NR, pl.G, a, pl.nbands * B, st))) return rc;
+    if (mark_pass1) cudaEventRecord(mark_pass1, st);
+    SVB_CUDA_CHECK(cudaStreamWaitEvent(st, ctx->ev_join, 0));
+    SelSumArgs q;
+    q.S1 = (const int16_t *)(ws + pl.off_S);
+    q.S2 = (const int16_t *)(ws + pl.off_S2);
+    q.a = a;
+    return launch_select_sum(NR, pl.G, q, pl.H, B, st);
 }
 
 // MODE_SGBM_3WAY (oracle: sgbm_3way_raw): four row stripes of ceil(H/4) rows, each started `overlap` rows early with

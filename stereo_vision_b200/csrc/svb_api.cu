@@ -42,6 +42,10 @@ extern "C" int svb_create(int device_id, svb_context **out)
     c->ev_valid = 0;
     c->job_valid = 0;
     c->job_stream = nullptr;
+    c->latency_off = 0;
+    cudaStreamCreateWithFlags(&c->aux, cudaStreamNonBlocking);
+    cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming);
     cudaEventCreateWithFlags(&c->job_done, cudaEventDisableTiming);
     for (int i = 0; i <= SVB_NUM_STAGES; i++) cudaEventCreate(&c->ev[i]);
     e = cudaMalloc(&c->tickets, 16 * sizeof(unsigned));
@@ -62,6 +66,9 @@ extern "C" int svb_destroy(svb_context *ctx)
     if (ctx->tickets) cudaFree(ctx->tickets);
     for (int i = 0; i <= SVB_NUM_STAGES; i++) cudaEventDestroy(ctx->ev[i]);
     cudaEventDestroy(ctx->job_done);
+    cudaEventDestroy(ctx->ev_fork);
+    cudaEventDestroy(ctx->ev_join);
+    cudaStreamDestroy(ctx->aux);
     delete ctx;
     return SVB_OK;
 }
@@ -87,7 +94,7 @@ static int next_pow2(int v)
     return p;
 }
 
-int svb_make_plan(const svb_sgbm_params *raw, int H, int W, int ch, SgbmPlan *pl)
+int svb_make_plan(const svb_sgbm_params *raw, int H, int W, int ch, int B, SgbmPlan *pl)
 {
     SVB_REQUIRE(raw && pl, SVB_ERR_INVALID, "sgbm: null argument");
     memset(pl, 0, sizeof *pl);
@@ -148,7 +155,17 @@ int svb_make_plan(const svb_sgbm_params *raw, int H, int W, int ch, SgbmPlan *pl
     take(SVB_SWEEP_MARGIN);
     pl->off_S = take(vol);
     take(SVB_SWEEP_MARGIN);
-    pl->off_edge = take((size_t)std::max(pl->nbands - 1, 1) * pl->W1 * 3 * pl->Dp * 2);
+    const size_t edge_bytes = (size_t)std::max(pl->nbands - 1, 1) * pl->W1 * 3 * pl->Dp * 2;
+    pl->off_edge = take(edge_bytes);
+    pl->latency = (p.mode == 0 || p.mode == 1) && (long long)B * pl->nbands <= SVB_LATENCY_MAX_BANDS;
+#ifdef SVB_NO_LATENCY_FORM
+    pl->latency = 0;
+#endif
+    if (pl->latency) {
+        pl->off_S2 = take(vol);
+        take(SVB_SWEEP_MARGIN);
+        pl->off_edge2 = take(edge_bytes);
+    }
     pl->off_prog = take(2 * sizeof(unsigned) * pl->nbands);
     pl->off_dpre = take((size_t)H * W * 2);
     pl->off_key = take((size_t)H * W * 4);
@@ -162,7 +179,7 @@ extern "C" int svb_sgbm_get_geometry(const svb_sgbm_params *raw, int W, int chan
 {
     SVB_REQUIRE(g, SVB_ERR_INVALID, "get_geometry: null argument");
     SgbmPlan pl;
-    int rc = svb_make_plan(raw, 16, W, channels, &pl);
+    int rc = svb_make_plan(raw, 4096, W, channels, 1, &pl);   // the height only matters to the workspace (and to mode 2's stripe check)
     if (rc) return rc;
     g->minX1 = pl.minX1; g->maxX1 = pl.maxX1; g->width1 = pl.W1; g->D = pl.D; g->Dp = pl.Dp;
     g->invalid16 = pl.invalid16; g->max_cost = pl.max_cost; g->safe_packed = pl.safe;
@@ -173,7 +190,7 @@ extern "C" int svb_sgbm_workspace_bytes(const svb_sgbm_params *raw, int H, int W
 {
     SVB_REQUIRE(bytes && B > 0, SVB_ERR_INVALID, "workspace_bytes: bad argument");
     SgbmPlan pl;
-    int rc = svb_make_plan(raw, H, W, channels, &pl);
+    int rc = svb_make_plan(raw, H, W, channels, B, &pl);
     if (rc) return rc;
     *bytes = pl.per_frame_bytes * (size_t)B;
     return SVB_OK;
@@ -230,10 +247,11 @@ extern "C" int svb_sgbm_compute(svb_context *ctx, const svb_sgbm_params *raw, co
     SVB_REQUIRE(ctx && left && right && disp, SVB_ERR_INVALID, "sgbm_compute: null argument");
     SVB_REQUIRE(B > 0, SVB_ERR_INVALID, "sgbm_compute: batch must be positive");
     SgbmPlan pl;
-    int rc = svb_make_plan(raw, H, W, channels, &pl);
+    int rc = svb_make_plan(raw, H, W, channels, B, &pl);
     if (rc) return rc;
     SVB_REQUIRE(pitch_bytes >= (size_t)W * channels && disp_pitch_elems >= (size_t)W, SVB_ERR_INVALID,
                 "sgbm_compute: pitch smaller than a row");
+    if (ctx->latency_off) pl.latency = 0;   // (the workspace layout keeps its slots; they are just not used)
     SVB_CUDA_CHECK(cudaSetDevice(ctx->device));
     cudaStream_t st = (cudaStream_t)stream;
     std::lock_guard<std::mutex> lock(ctx->mu);
@@ -252,9 +270,14 @@ extern "C" int svb_sgbm_compute(svb_context *ctx, const svb_sgbm_params *raw, co
     } else {
         if ((rc = svb_launch_cost(pl, ws, pl.per_frame_bytes, B, 0, pl.H, st))) return rc;
         SVB_MARK(2);
-        if ((rc = svb_launch_aggregate(ctx, pl, ws, pl.per_frame_bytes, B, 1, st))) return rc;
-        SVB_MARK(3);
-        if ((rc = svb_launch_aggregate(ctx, pl, ws, pl.per_frame_bytes, B, 2, st))) return rc;
+        if (pl.latency) {   // both sweeps side by side, then sum + selection (mark 3 = end of the forward sweep)
+            if ((rc = svb_launch_aggregate_concurrent(ctx, pl, ws, pl.per_frame_bytes, B, st, ctx->timing ? ctx->ev[3] : nullptr)))
+                return rc;
+        } else {
+            if ((rc = svb_launch_aggregate(ctx, pl, ws, pl.per_frame_bytes, B, 1, st))) return rc;
+            SVB_MARK(3);
+            if ((rc = svb_launch_aggregate(ctx, pl, ws, pl.per_frame_bytes, B, 2, st))) return rc;
+        }
     }
     SVB_MARK(4);
     if ((rc = svb_launch_lrcheck(pl, ws, pl.per_frame_bytes, B, st))) return rc;
@@ -275,6 +298,13 @@ extern "C" int svb_sgbm_compute(svb_context *ctx, const svb_sgbm_params *raw, co
 // Per-stage device times (ms) of the last svb_sgbm_compute on this context, measured with CUDA events recorded
 // on the caller's stream: [planes, cost, aggregate pass 1, aggregate pass 2 + selection, LR check + median,
 // speckle].  Blocks until that call has finished.  Enable with svb_set_timing(ctx, 1).
+extern "C" int svb_set_latency_form(svb_context *ctx, int enable)
+{
+    SVB_REQUIRE(ctx, SVB_ERR_INVALID, "set_latency_form: null context");
+    std::lock_guard<std::mutex> lock(ctx->mu);
+    ctx->latency_off = !enable;
+    return SVB_OK;
+}
 extern "C" int svb_set_timing(svb_context *ctx, int enable)
 {
     SVB_REQUIRE(ctx, SVB_ERR_INVALID, "set_timing: null context");
@@ -297,7 +327,7 @@ extern "C" int svb_sgbm_debug_stages(svb_context *ctx, const svb_sgbm_params *ra
 {
     SVB_REQUIRE(ctx && left && right, SVB_ERR_INVALID, "sgbm_debug_stages: null argument");
     SgbmPlan pl;
-    int rc = svb_make_plan(raw, H, W, channels, &pl);
+    int rc = svb_make_plan(raw, H, W, channels, 1, &pl);
     if (rc) return rc;
     SVB_CUDA_CHECK(cudaSetDevice(ctx->device));
     cudaStream_t st = (cudaStream_t)stream;

@@ -47,6 +47,9 @@ struct svb_context {
     cudaEvent_t job_done;
     cudaStream_t job_stream;
     int job_valid;
+    int latency_off;        // svb_set_latency_form(ctx, 0): always run the two sweeps back to back
+    cudaStream_t aux;       // second stream of the latency form (forked from / joined to the caller's stream by events)
+    cudaEvent_t ev_fork, ev_join;
     int timing;             // record per-stage events in svb_sgbm_compute
     cudaEvent_t ev[SVB_NUM_STAGES + 1];
     int ev_valid;
@@ -68,14 +71,22 @@ struct SgbmPlan {
     int nbands;
     // workspace layout (bytes, per frame)
     size_t off_lplanes, off_rplanes, off_C, off_S, off_edge, off_prog, off_dpre, off_key, off_dtmp, off_labels;
+    // Latency form (few pairs in flight: B * nbands <= SVB_LATENCY_MAX_BANDS, modes 0 and 1): the reverse sweep runs
+    // concurrently with the forward one on a second stream, writes its own sum S2 through its own band-edge buffer, and
+    // k_select_sum adds the two volumes and selects.  Costs one more volume + edge buffer per pair, halves the wavefront
+    // time a single pair waits for.
+    int latency;
+    size_t off_S2, off_edge2;
     size_t per_frame_bytes;
     int Wr;              // right-plane row length (elements) incl. padding
 };
 
 // unclamped prefetch reach of k_sweep around the C / S volumes: (lag_last + AGG_UNROLL + PFD) * Dp * 2 bytes <= 62 KB
 #define SVB_SWEEP_MARGIN (64 << 10)
+#define SVB_LATENCY_MAX_BANDS 74    // 2 x 74 bands: both sweeps of a job this small fit the GPU's 148 SMs side by side
 
-int svb_make_plan(const svb_sgbm_params *raw, int H, int W, int ch, SgbmPlan *plan);
+// B: pairs processed together (decides the latency form: SgbmPlan::latency)
+int svb_make_plan(const svb_sgbm_params *raw, int H, int W, int ch, int B, SgbmPlan *plan);
 
 static inline size_t svb_align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
@@ -86,6 +97,9 @@ int svb_launch_cost(const SgbmPlan &pl, char *ws, size_t ws_stride, int B, int y
 // passes: bit 0 = pass 1 (4 forward paths), bit 1 = pass 2 (remaining paths + selection)
 int svb_launch_aggregate(svb_context *ctx, const SgbmPlan &pl, char *ws, size_t ws_stride, int B, int passes,
                          cudaStream_t st);
+// latency form: both sweeps concurrently (st + ctx->aux), then the sum + selection kernel
+int svb_launch_aggregate_concurrent(svb_context *ctx, const SgbmPlan &pl, char *ws, size_t ws_stride, int B, cudaStream_t st,
+                                    cudaEvent_t mark_pass1);
 // MODE_SGBM_3WAY: cost volume + aggregation + selection, stripe by stripe
 int svb_launch_cost_aggregate_3way(svb_context *ctx, const SgbmPlan &pl, char *ws, size_t ws_stride, int B, cudaStream_t st);
 int svb_launch_lrcheck(const SgbmPlan &pl, char *ws, size_t ws_stride, int B, cudaStream_t st);

@@ -30,26 +30,38 @@ def test_cost_volume_and_pass1_match_oracle(sv):
         assert np.array_equal(raw_g, raw_o), f"pre-median disparity mismatch {H}x{W} D={D}"
 
 
-def test_small_sweep_matches_cv2_golden_and_oracle(sv, golden):
-    bad = []
-    for i, c in enumerate(cases.sgbm_small_cases()):
-        L, R = cases.sgbm_inputs(c)
-        got = sv.StereoSGBM_create(**c["kw"]).compute(L, R)
-        assert got.dtype == np.int16 and got.shape == L.shape[:2]
-        if not np.array_equal(got, golden[f"sgbm_{i}"]):
-            bad.append((i, c, int((got != golden[f"sgbm_{i}"]).sum())))
-    assert not bad, f"{len(bad)} of 96 cases differ from cv2 golden: {bad[:3]}"
+@pytest.mark.parametrize("latency_form", [True, False])
+def test_small_sweep_matches_cv2_golden_and_oracle(sv, golden, latency_form):
+    """96 cv2 golden cases through both schedules of the aggregation: the latency form (the two sweeps side by side +
+    k_select_sum: what a single pair gets by default) and the back-to-back form with the fused selection."""
+    sv.set_latency_form(latency_form)
+    try:
+        bad = []
+        for i, c in enumerate(cases.sgbm_small_cases()):
+            L, R = cases.sgbm_inputs(c)
+            got = sv.StereoSGBM_create(**c["kw"]).compute(L, R)
+            assert got.dtype == np.int16 and got.shape == L.shape[:2]
+            if not np.array_equal(got, golden[f"sgbm_{i}"]):
+                bad.append((i, c, int((got != golden[f"sgbm_{i}"]).sum())))
+        assert not bad, f"{len(bad)} of 96 cases differ from cv2 golden (latency_form={latency_form}): {bad[:3]}"
+    finally:
+        sv.set_latency_form(True)
 
 
+@pytest.mark.parametrize("latency_form", [True, False])
 @pytest.mark.parametrize("name", ["c1", "c2", "c3", "c3_sgbm"])
-def test_full_size_matches_cv2_golden_hash(sv, golden_full, name):
+def test_full_size_matches_cv2_golden_hash(sv, golden_full, name, latency_form):
     L, R, kw = cases.full_inputs(name)
     g = golden_full["full"][name]
     assert [_sha(L), _sha(R)] == g["in_sha256"], "synthetic inputs are not reproducible on this host"
-    got = sv.StereoSGBM_create(**kw).compute(L, R)
+    sv.set_latency_form(latency_form)
+    try:
+        got = sv.StereoSGBM_create(**kw).compute(L, R)
+    finally:
+        sv.set_latency_form(True)
     if _sha(got) != g["sha256"]:
         ref = oracle.sgbm_compute(L, R, **kw)
-        raise AssertionError(f"{name}: differs from cv2 golden; vs oracle: {(got != ref).sum()} px differ")
+        raise AssertionError(f"{name} (latency_form={latency_form}): differs from cv2 golden; vs oracle: {(got != ref).sum()} px differ")
 
 
 def test_full_size_c5_4k(sv, golden_full):
@@ -275,3 +287,35 @@ def test_c3_batch_of_32_distinct_frames_matches_cv2_hashes(sv, golden_r2):
     bad = [i for i in range(s1 - s0) if _sha(out[i]) != c["sha256"][i]]
     assert not bad, f"frames {bad} of the 32-frame batch differ from cv2"
     sv.release_workspaces()
+
+
+def test_workspace_guards_stay_intact(sv):
+    """Out-of-bounds WRITE check of our own (compute-sanitizer is closed on this pool): the caller-owned workspace and
+    the output are embedded in larger buffers filled with a pattern; after compute the guard bytes must be untouched and
+    the result must equal the oracle's.  Runs the single-pair latency form and a batch in the back-to-back form."""
+    import ctypes as C
+    import torch
+    from stereo_vision_b200 import _lib
+    lib, ctx = _lib.load(), _lib.context(0)
+    GUARD = 1 << 20
+    for (H, W, D, B, mode) in [(45, 400, 256, 1, 1), (45, 400, 256, 12, 1), (64, 300, 96, 3, 0), (70, 330, 128, 2, 2)]:
+        kw = synth.sgbm_kwargs(D, 5, mode)
+        pairs = [synth.stereo_pair(H, W, D, seed=50 + i) for i in range(B)]
+        Lb = torch.from_numpy(np.stack([p[0] for p in pairs])).cuda()
+        Rb = torch.from_numpy(np.stack([p[1] for p in pairs])).cuda()
+        prm = _lib.SgbmParams(*[kw[k] for k in ("minDisparity", "numDisparities", "blockSize", "P1", "P2", "disp12MaxDiff",
+                                                "preFilterCap", "uniquenessRatio", "speckleWindowSize", "speckleRange", "mode")])
+        need = C.c_size_t()
+        assert lib.svb_sgbm_workspace_bytes(C.byref(prm), H, W, 1, B, C.byref(need)) == 0
+        ws = torch.full((need.value + 2 * GUARD,), 0xA5, dtype=torch.uint8, device="cuda")
+        out = torch.full((B * H * W + 2 * GUARD,), 0x5A5A, dtype=torch.int16, device="cuda")
+        rc = lib.svb_sgbm_compute(ctx, C.byref(prm), Lb.data_ptr(), Rb.data_ptr(), H, W, 1, W, H * W, B,
+                                  out.data_ptr() + 2 * GUARD, W, H * W, ws.data_ptr() + GUARD, need.value,
+                                  torch.cuda.current_stream().cuda_stream)
+        assert rc == 0, lib.svb_last_error()
+        torch.cuda.synchronize()
+        assert bool((ws[:GUARD] == 0xA5).all()) and bool((ws[GUARD + need.value:] == 0xA5).all()), (H, W, D, B, mode)
+        assert bool((out[:GUARD] == 0x5A5A).all()) and bool((out[GUARD + B * H * W:] == 0x5A5A).all()), (H, W, D, B, mode)
+        got = out[GUARD:GUARD + B * H * W].reshape(B, H, W).cpu().numpy()
+        for i, (l, r) in enumerate(pairs):
+            assert np.array_equal(got[i], oracle.sgbm_compute(l, r, **kw)), (H, W, D, B, mode, i)

@@ -7,6 +7,8 @@
 #include <vector>
 int svb_launch_aggregate(svb_context *, const SgbmPlan &, char *, size_t, int, int, cudaStream_t) { return 0; }
 int svb_launch_lrcheck(const SgbmPlan &, char *, size_t, int, cudaStream_t) { return 0; }
+int svb_launch_aggregate_concurrent(svb_context *, const SgbmPlan &, char *, size_t, int, cudaStream_t, cudaEvent_t) { return 0; }
+int svb_launch_cost_aggregate_3way(svb_context *, const SgbmPlan &, char *, size_t, int, cudaStream_t) { return 0; }
 int svb_launch_median3(const int16_t *, int16_t *, int, int, size_t, size_t, size_t, size_t, int, cudaStream_t) { return 0; }
 int svb_launch_speckle(int16_t *, int, int, size_t, size_t, int, int, int, int, int32_t *, size_t, cudaStream_t) { return 0; }
 
@@ -26,7 +28,7 @@ int main(int argc, char **argv)
     p.minDisparity = 0; p.numDisparities = D; p.blockSize = bs; p.P1 = 8 * ch * bs * bs; p.P2 = 32 * ch * bs * bs;
     p.disp12MaxDiff = 1; p.preFilterCap = 31; p.uniquenessRatio = 10; p.speckleWindowSize = 100; p.speckleRange = 2; p.mode = 1;
     SgbmPlan pl;
-    if (svb_make_plan(&p, H, W, ch, &pl)) { printf("plan: %s\n", svb_last_error()); return 1; }
+    if (svb_make_plan(&p, H, W, ch, B, &pl)) { printf("plan: %s\n", svb_last_error()); return 1; }
     const size_t img = (size_t)H * W * ch;
     std::vector<uint8_t> hl(img * B), hr(img * B);
     uint32_t s = 12345;

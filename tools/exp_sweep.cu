@@ -27,7 +27,7 @@ int main(int argc, char **argv)
     a.keys = (unsigned *)(ws + 2 * vol + edge + 4096 + (size_t)H * W * 2);
     a.ws_stride = (argc > 4 && atoi(argv[4])) ? 0 : stride;   // hot: every frame aliases frame 0 (L2-resident)
     a.H = H; a.W = W; a.W1 = W1; a.D = 256; a.Dp = Dp; a.minX1 = 256; a.minD = 0;
-    a.nbands = NB; a.B = B; a.P1d = 200 * 0x10001u; a.P2d = 800 * 0x10001u; a.uniq = 10; a.one = 1; a.k16 = 65536; a.pubmask = B > 1 ? 7 : 1; a.invalid16 = -16; a.slack = argc > 3 ? atoi(argv[3]) : 0;
+    a.nbands = NB; a.B = B; a.P1d = 200 * 0x10001u; a.P2d = 800 * 0x10001u; a.uniq = 10; a.one = 1; a.k16 = 65536; a.pubmask = argc > 5 ? atoi(argv[5]) - 1 : (B > 1 ? 7 : 1); a.invalid16 = -16; a.slack = argc > 3 ? atoi(argv[3]) : 0;
     cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
     for (int pass = 0; pass < 2; pass++) {
         float best = 1e9;
