@@ -560,8 +560,12 @@ __device__ __forceinline__ void cta_barrier() { asm volatile("bar.sync 0;" ::: "
 // NV = 3: wavefront sweep with the three vertical/diagonal predecessors (+ one DMA warp per CTA);
 // NV = 1: same machinery, vertical predecessor only (MODE_HH4: 2 + 2 paths);
 // NV = 0: horizontal path only (rows independent; the 5th path of MODE_SGBM), no barriers, no DMA warp.
-template <int NR, int G, int NGRP, int NV, bool PASS2, bool SAFE, bool PAD, int PFD, bool REV = PASS2>
-__global__ void __launch_bounds__(NGRP *G + (NV ? 32 : 0)) k_sweep(const __grid_constant__ AggArgs a)
+// MINB: minimum CTAs per SM handed to ptxas (0 = unconstrained).  Only the Dp = 128 kernels (G = 16, 288 threads) have a
+// second instantiation with MINB = 2: 112 instead of 140-144 registers, two CTAs per SM — faster with many bands in flight
+// (c2 MODE_HH at B = 32: pass 1 7.1 -> 5.6 ms, pass 2 10.9 -> 8.2 ms; B = 16: 3.82 -> 3.48 / 6.01 -> 5.13), slower with few
+// (B = 12: pass 1 3.10 -> 3.29; B = 8: 2.34 -> 3.14 ms), so the launcher picks by grid size (AGG_MINB2_GRID).
+template <int NR, int G, int NGRP, int NV, bool PASS2, bool SAFE, bool PAD, int PFD, bool REV = PASS2, int MINB = 0>
+__global__ void __launch_bounds__(NGRP *G + (NV ? 32 : 0), MINB) k_sweep(const __grid_constant__ AggArgs a)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     typedef SweepSmem<NGRP, NV, PASS2> SM;
@@ -773,7 +777,10 @@ __global__ void __launch_bounds__(NGRP *G + (NV ? 32 : 0)) k_sweep(const __grid_
 }
 
 // ---------------- host side ----------------
-template <int NR, int G, int NGRP, int NV, bool PASS2, bool SAFE, bool PAD, bool REV = PASS2>
+#ifndef AGG_MINB2_GRID
+#define AGG_MINB2_GRID (4 * 148)   // CTAs from which the two-CTAs-per-SM instantiation of the Dp = 128 kernels is used
+#endif
+template <int NR, int G, int NGRP, int NV, bool PASS2, bool SAFE, bool PAD, bool REV = PASS2, int MINB = 0>
 static int launch_sweep_t(const AggArgs &a, int ngrid, cudaStream_t st)
 {
 #ifndef AGG_PFD2
@@ -781,7 +788,7 @@ static int launch_sweep_t(const AggArgs &a, int ngrid, cudaStream_t st)
 #endif
     constexpr int PFD = NR == 4 ? (PASS2 ? AGG_PFD2 : 4) : 2;   // C prefetch depth in pixels (pass 2 is short of registers)
     const size_t smem = SweepSmem<NGRP, NV, PASS2>::bytes(a.Dp, 2 * NR);
-    auto kern = k_sweep<NR, G, NGRP, NV, PASS2, SAFE, PAD, PFD, REV>;
+    auto kern = k_sweep<NR, G, NGRP, NV, PASS2, SAFE, PAD, PFD, REV, MINB>;
     // the opt-in is per device and per function; setting it on every launch is cheap and stays correct with several
     // devices / host threads in one process
     SVB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -798,7 +805,8 @@ static int launch_sweep_g(int NR, int G, const AggArgs &a, int ngrid, cudaStream
     case 2: return launch_sweep_t<4, 2, 16, NV, PASS2, SAFE, PAD, REV>(a, ngrid, st);
     case 4: return launch_sweep_t<4, 4, 16, NV, PASS2, SAFE, PAD, REV>(a, ngrid, st);
     case 8: return launch_sweep_t<4, 8, 16, NV, PASS2, SAFE, PAD, REV>(a, ngrid, st);
-    case 16: return launch_sweep_t<4, 16, 16, NV, PASS2, SAFE, PAD, REV>(a, ngrid, st);
+    case 16: return (NV && ngrid >= AGG_MINB2_GRID) ? launch_sweep_t<4, 16, 16, NV, PASS2, SAFE, PAD, REV, 2>(a, ngrid, st)
+                                                    : launch_sweep_t<4, 16, 16, NV, PASS2, SAFE, PAD, REV>(a, ngrid, st);
     default: return launch_sweep_t<4, 32, 15, NV, PASS2, SAFE, PAD, REV>(a, ngrid, st);
     }
 }

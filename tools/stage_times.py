@@ -21,13 +21,14 @@ def run(name, H, W, D, bs, mode, B, n=3):
     tot = sum(acc.values()) / n
     print(f"{name} B={B}: total {tot:.3f} ms ({tot/B:.3f}/frame) " + " ".join(f"{k}={v/n:.3f}" for k, v in acc.items()), flush=True)
 
-B = int(sys.argv[1]) if len(sys.argv) > 1 else 0
-if B:
-    run("c3 HH", 1080, 1920, 256, 5, 1, B, n=2)
-else:
-    for B in (1, 8):
-        run("c1 SGBM", 480, 640, 64, 5, 0, B)
-        run("c2 SGBM", 720, 1280, 128, 5, 0, B)
-        run("c3 HH", 1080, 1920, 256, 5, 1, B)
-        run("c3 SGBM", 1080, 1920, 256, 5, 0, B)
-    run("c5 4K SGBM", 2160, 3840, 256, 7, 0, 1)
+if __name__ == "__main__":
+    B = int(sys.argv[1]) if len(sys.argv) > 1 else 0
+    if B:
+        run("c3 HH", 1080, 1920, 256, 5, 1, B, n=2)
+    else:
+        for B in (1, 8):
+            run("c1 SGBM", 480, 640, 64, 5, 0, B)
+            run("c2 SGBM", 720, 1280, 128, 5, 0, B)
+            run("c3 HH", 1080, 1920, 256, 5, 1, B)
+            run("c3 SGBM", 1080, 1920, 256, 5, 0, B)
+        run("c5 4K SGBM", 2160, 3840, 256, 7, 0, 1)
