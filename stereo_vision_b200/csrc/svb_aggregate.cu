@@ -53,7 +53,7 @@
 // (EPF = SLOTS - PPS - 2 = 2 while row 0 needs pixels <= t+PPS: every cp.async has to land within its own barrier
 // interval).  That holds for the long intervals of Dp >= 256 because the vectors were prefetched into L2 (AGG_L2PF);
 // with the short intervals of Dp = 128 it made pass 1 25 % slower, hence the compile-time switch.
-#define AGG_EDGE_LIKE_ROW(G) ((G) == 32)
+#define AGG_EDGE_LIKE_ROW(G) ((G) == 32 && NR >= 4)   // (NR: the enclosing template parameter)
 #define AGG_UNROLL 12      // pixel-times per loop iteration: a multiple of SLOTS, ENS, PPS and the prefetch depths
 #ifndef AGG_PUB
 #define AGG_PUB 8          // publish cross-band progress every AGG_PUB pixels (a single frame in flight: every AGG_PPS)
@@ -234,6 +234,8 @@ __device__ __forceinline__ void finish_pair(uint32_t (&LA)[NR], uint32_t (&LB)[N
     }
 }
 
+// Vector moves of a lane's NR packed registers (E = 2*NR disparities): 16-byte pieces for NR = 4 / 8, one 8- or 4-byte
+// piece for the wide-lane layouts NR = 2 / 1 (32 lanes per row at Dp = 128 / 64, used by the latency form).
 template <int NR>
 __device__ __forceinline__ void ld_regs_shared(const int16_t *p, uint32_t (&r)[NR])
 {
@@ -242,6 +244,8 @@ __device__ __forceinline__ void ld_regs_shared(const int16_t *p, uint32_t (&r)[N
         const uint4 v = reinterpret_cast<const uint4 *>(p)[q];
         r[4 * q] = v.x; r[4 * q + 1] = v.y; r[4 * q + 2] = v.z; r[4 * q + 3] = v.w;
     }
+    if (NR == 2) { const uint2 v = *reinterpret_cast<const uint2 *>(p); r[0] = v.x; r[NR - 1] = v.y; }
+    if (NR == 1) r[0] = *reinterpret_cast<const uint32_t *>(p);
 }
 template <int NR>
 __device__ __forceinline__ void st_regs(int16_t *p, const uint32_t (&r)[NR])
@@ -249,6 +253,8 @@ __device__ __forceinline__ void st_regs(int16_t *p, const uint32_t (&r)[NR])
 #pragma unroll
     for (int q = 0; q < NR / 4; q++)
         reinterpret_cast<uint4 *>(p)[q] = make_uint4(r[4 * q], r[4 * q + 1], r[4 * q + 2], r[4 * q + 3]);
+    if (NR == 2) *reinterpret_cast<uint2 *>(p) = make_uint2(r[0], r[NR - 1]);
+    if (NR == 1) *reinterpret_cast<uint32_t *>(p) = r[0];
 }
 template <int NR>
 __device__ __forceinline__ void ld_regs_stream(const int16_t *p, uint32_t (&r)[NR])
@@ -258,15 +264,10 @@ __device__ __forceinline__ void ld_regs_stream(const int16_t *p, uint32_t (&r)[N
         const uint4 v = __ldcs(reinterpret_cast<const uint4 *>(p) + q);
         r[4 * q] = v.x; r[4 * q + 1] = v.y; r[4 * q + 2] = v.z; r[4 * q + 3] = v.w;
     }
+    if (NR == 2) { const uint2 v = __ldcs(reinterpret_cast<const uint2 *>(p)); r[0] = v.x; r[NR - 1] = v.y; }
+    if (NR == 1) r[0] = __ldcs(reinterpret_cast<const uint32_t *>(p));
 }
-template <int NR>
-__device__ __forceinline__ void st_regs_cg(int16_t *p, const uint32_t (&r)[NR])
-{
-#pragma unroll
-    for (int q = 0; q < NR / 4; q++)
-        __stcg(reinterpret_cast<uint4 *>(p) + q, make_uint4(r[4 * q], r[4 * q + 1], r[4 * q + 2], r[4 * q + 3]));
-}
-// predicated 16-byte global stores (no branch: keeps the four directions of a step in one basic block)
+// predicated global stores (no branch: keeps the four directions of a step in one basic block)
 __device__ __forceinline__ void st_cg_pred(void *p, uint32_t a, uint32_t b, uint32_t c, uint32_t d, bool pred)
 {
     asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.s32 p, %5, 0;\n\t@p st.global.cg.v4.u32 [%0], {%1, %2, %3, %4};\n\t}"
@@ -277,12 +278,26 @@ __device__ __forceinline__ void st_cs_pred(void *p, uint32_t a, uint32_t b, uint
     asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.s32 p, %5, 0;\n\t@p st.global.cs.v4.u32 [%0], {%1, %2, %3, %4};\n\t}"
                  ::"l"(p), "r"(a), "r"(b), "r"(c), "r"(d), "r"((int)pred) : "memory");
 }
+template <bool CS>   // 8- and 4-byte forms (CS: streaming, else cache-global)
+__device__ __forceinline__ void st_pred2(void *p, uint32_t a, uint32_t b, bool pred)
+{
+    if (CS) asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.s32 p, %3, 0;\n\t@p st.global.cs.v2.u32 [%0], {%1, %2};\n\t}" ::"l"(p), "r"(a), "r"(b), "r"((int)pred) : "memory");
+    else asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.s32 p, %3, 0;\n\t@p st.global.cg.v2.u32 [%0], {%1, %2};\n\t}" ::"l"(p), "r"(a), "r"(b), "r"((int)pred) : "memory");
+}
+template <bool CS>
+__device__ __forceinline__ void st_pred1(void *p, uint32_t a, bool pred)
+{
+    if (CS) asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.s32 p, %2, 0;\n\t@p st.global.cs.u32 [%0], %1;\n\t}" ::"l"(p), "r"(a), "r"((int)pred) : "memory");
+    else asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.s32 p, %2, 0;\n\t@p st.global.cg.u32 [%0], %1;\n\t}" ::"l"(p), "r"(a), "r"((int)pred) : "memory");
+}
 template <int NR>
 __device__ __forceinline__ void st_regs_cg_pred(int16_t *p, const uint32_t (&r)[NR], bool pred)
 {
 #pragma unroll
     for (int q = 0; q < NR / 4; q++)
         st_cg_pred(reinterpret_cast<uint4 *>(p) + q, r[4 * q], r[4 * q + 1], r[4 * q + 2], r[4 * q + 3], pred);
+    if (NR == 2) st_pred2<false>(p, r[0], r[NR - 1], pred);
+    if (NR == 1) st_pred1<false>(p, r[0], pred);
 }
 template <int NR>
 __device__ __forceinline__ void st_regs_cs_pred(int16_t *p, const uint32_t (&r)[NR], bool pred)
@@ -290,13 +305,8 @@ __device__ __forceinline__ void st_regs_cs_pred(int16_t *p, const uint32_t (&r)[
 #pragma unroll
     for (int q = 0; q < NR / 4; q++)
         st_cs_pred(reinterpret_cast<uint4 *>(p) + q, r[4 * q], r[4 * q + 1], r[4 * q + 2], r[4 * q + 3], pred);
-}
-template <int NR>
-__device__ __forceinline__ void st_regs_stream(int16_t *p, const uint32_t (&r)[NR])
-{
-#pragma unroll
-    for (int q = 0; q < NR / 4; q++)
-        __stcs(reinterpret_cast<uint4 *>(p) + q, make_uint4(r[4 * q], r[4 * q + 1], r[4 * q + 2], r[4 * q + 3]));
+    if (NR == 2) st_pred2<true>(p, r[0], r[NR - 1], pred);
+    if (NR == 1) st_pred1<true>(p, r[0], pred);
 }
 
 // ---- pass-2 tail, lane-parallel: lane holds one parked pixel (first loop) ----
@@ -786,7 +796,7 @@ static int launch_sweep_t(const AggArgs &a, int ngrid, cudaStream_t st)
 #ifndef AGG_PFD2
 #define AGG_PFD2 4
 #endif
-    constexpr int PFD = NR == 4 ? (PASS2 ? AGG_PFD2 : 4) : 2;   // C prefetch depth in pixels (pass 2 is short of registers)
+    constexpr int PFD = NR <= 4 ? (PASS2 ? AGG_PFD2 : 4) : 2;   // C prefetch depth in pixels (pass 2 is short of registers)
     const size_t smem = SweepSmem<NGRP, NV, PASS2>::bytes(a.Dp, 2 * NR);
     auto kern = k_sweep<NR, G, NGRP, NV, PASS2, SAFE, PAD, PFD, REV, MINB>;
     // the opt-in is per device and per function; setting it on every launch is cheap and stays correct with several
@@ -801,6 +811,14 @@ template <int NV, bool PASS2, bool SAFE, bool PAD, bool REV>
 static int launch_sweep_g(int NR, int G, const AggArgs &a, int ngrid, cudaStream_t st)
 {
     if (NR == 8) return launch_sweep_t<8, 32, 7, NV, PASS2, SAFE, PAD, REV>(a, ngrid, st);
+    if (NR < 4) {   // wide-lane layouts of the latency form (a whole warp per row at Dp = 64 / 128): store-S sweeps only
+        if constexpr (!PASS2 && NV != 1) {
+            if (NR == 1 && G == 32) return launch_sweep_t<1, 32, 15, NV, PASS2, SAFE, PAD, REV>(a, ngrid, st);
+            if (NR == 2 && G == 32) return launch_sweep_t<2, 32, 15, NV, PASS2, SAFE, PAD, REV>(a, ngrid, st);
+        }
+        svb_set_error("sweep: no kernel for NR=%d G=%d in this family", NR, G);
+        return SVB_ERR_UNSUPPORTED;
+    }
     switch (G) {
     case 2: return launch_sweep_t<4, 2, 16, NV, PASS2, SAFE, PAD, REV>(a, ngrid, st);
     case 4: return launch_sweep_t<4, 4, 16, NV, PASS2, SAFE, PAD, REV>(a, ngrid, st);
@@ -939,6 +957,8 @@ static int launch_select_sum_t(const SelSumArgs &q, int H, int B, cudaStream_t s
 static int launch_select_sum(int NR, int G, const SelSumArgs &q, int H, int B, cudaStream_t st)
 {
     if (NR == 8) return launch_select_sum_t<8, 32>(q, H, B, st);
+    if (NR == 1) return launch_select_sum_t<1, 32>(q, H, B, st);
+    if (NR == 2) return launch_select_sum_t<2, 32>(q, H, B, st);
     switch (G) {
     case 2: return launch_select_sum_t<4, 2>(q, H, B, st);
     case 4: return launch_select_sum_t<4, 4>(q, H, B, st);

@@ -94,7 +94,7 @@ static int next_pow2(int v)
     return p;
 }
 
-int svb_make_plan(const svb_sgbm_params *raw, int H, int W, int ch, int B, SgbmPlan *pl)
+int svb_make_plan(const svb_sgbm_params *raw, int H, int W, int ch, int B, int latency_ok, SgbmPlan *pl)
 {
     SVB_REQUIRE(raw && pl, SVB_ERR_INVALID, "sgbm: null argument");
     memset(pl, 0, sizeof *pl);
@@ -142,6 +142,20 @@ int svb_make_plan(const svb_sgbm_params *raw, int H, int W, int ch, int B, SgbmP
     pl->Dp = pl->E * pl->G;
     pl->NG = pl->G == 32 ? (pl->E == 16 ? 7 : 15) : 16;   // rows per band (must match the k_sweep instantiation)
     pl->nbands = (H + pl->NG - 1) / pl->NG;
+    // Latency form (SgbmPlan::latency): small jobs only.  At Dp = 64 / 128 it also switches to the wide-lane layout — a
+    // whole warp per row with 2 / 4 disparities per lane instead of 8 / 16 lanes with 8: a single pair is bound by the
+    // dependent instruction stream of one warp per scheduler, and a quarter of the per-lane work shortens it.
+    pl->latency = 0;
+#ifndef SVB_NO_LATENCY_FORM
+    if (latency_ok && (p.mode == 0 || p.mode == 1)) {
+        const bool wide = pl->Dp == 64 || pl->Dp == 128;
+        const int ng = wide ? 15 : pl->NG, nb = (H + ng - 1) / ng;
+        if ((long long)B * nb <= SVB_LATENCY_MAX_BANDS) {
+            pl->latency = 1;
+            if (wide) { pl->G = 32; pl->E = pl->Dp / 32; pl->NG = ng; pl->nbands = nb; }
+        }
+    }
+#endif
     pl->Wr = (int)svb_align_up((size_t)W + pl->Dp + 8, 8);
     size_t off = 0;
     auto take = [&](size_t bytes) { size_t o = off; off = svb_align_up(off + std::max<size_t>(bytes, 16), 256); return o; };
@@ -157,10 +171,6 @@ int svb_make_plan(const svb_sgbm_params *raw, int H, int W, int ch, int B, SgbmP
     take(SVB_SWEEP_MARGIN);
     const size_t edge_bytes = (size_t)std::max(pl->nbands - 1, 1) * pl->W1 * 3 * pl->Dp * 2;
     pl->off_edge = take(edge_bytes);
-    pl->latency = (p.mode == 0 || p.mode == 1) && (long long)B * pl->nbands <= SVB_LATENCY_MAX_BANDS;
-#ifdef SVB_NO_LATENCY_FORM
-    pl->latency = 0;
-#endif
     if (pl->latency) {
         pl->off_S2 = take(vol);
         take(SVB_SWEEP_MARGIN);
@@ -179,7 +189,7 @@ extern "C" int svb_sgbm_get_geometry(const svb_sgbm_params *raw, int W, int chan
 {
     SVB_REQUIRE(g, SVB_ERR_INVALID, "get_geometry: null argument");
     SgbmPlan pl;
-    int rc = svb_make_plan(raw, 4096, W, channels, 1, &pl);   // the height only matters to the workspace (and to mode 2's stripe check)
+    int rc = svb_make_plan(raw, 4096, W, channels, 1, 0, &pl);   // the height only matters to the workspace (and to mode 2's stripe check)
     if (rc) return rc;
     g->minX1 = pl.minX1; g->maxX1 = pl.maxX1; g->width1 = pl.W1; g->D = pl.D; g->Dp = pl.Dp;
     g->invalid16 = pl.invalid16; g->max_cost = pl.max_cost; g->safe_packed = pl.safe;
@@ -190,7 +200,7 @@ extern "C" int svb_sgbm_workspace_bytes(const svb_sgbm_params *raw, int H, int W
 {
     SVB_REQUIRE(bytes && B > 0, SVB_ERR_INVALID, "workspace_bytes: bad argument");
     SgbmPlan pl;
-    int rc = svb_make_plan(raw, H, W, channels, B, &pl);
+    int rc = svb_make_plan(raw, H, W, channels, B, 1, &pl);   // (the latency form's layout is the larger one)
     if (rc) return rc;
     *bytes = pl.per_frame_bytes * (size_t)B;
     return SVB_OK;
@@ -247,11 +257,10 @@ extern "C" int svb_sgbm_compute(svb_context *ctx, const svb_sgbm_params *raw, co
     SVB_REQUIRE(ctx && left && right && disp, SVB_ERR_INVALID, "sgbm_compute: null argument");
     SVB_REQUIRE(B > 0, SVB_ERR_INVALID, "sgbm_compute: batch must be positive");
     SgbmPlan pl;
-    int rc = svb_make_plan(raw, H, W, channels, B, &pl);
+    int rc = svb_make_plan(raw, H, W, channels, B, !ctx->latency_off, &pl);
     if (rc) return rc;
     SVB_REQUIRE(pitch_bytes >= (size_t)W * channels && disp_pitch_elems >= (size_t)W, SVB_ERR_INVALID,
                 "sgbm_compute: pitch smaller than a row");
-    if (ctx->latency_off) pl.latency = 0;   // (the workspace layout keeps its slots; they are just not used)
     SVB_CUDA_CHECK(cudaSetDevice(ctx->device));
     cudaStream_t st = (cudaStream_t)stream;
     std::lock_guard<std::mutex> lock(ctx->mu);
@@ -327,7 +336,7 @@ extern "C" int svb_sgbm_debug_stages(svb_context *ctx, const svb_sgbm_params *ra
 {
     SVB_REQUIRE(ctx && left && right, SVB_ERR_INVALID, "sgbm_debug_stages: null argument");
     SgbmPlan pl;
-    int rc = svb_make_plan(raw, H, W, channels, 1, &pl);
+    int rc = svb_make_plan(raw, H, W, channels, 1, 0, &pl);   // the taps come from the back-to-back schedule
     if (rc) return rc;
     SVB_CUDA_CHECK(cudaSetDevice(ctx->device));
     cudaStream_t st = (cudaStream_t)stream;

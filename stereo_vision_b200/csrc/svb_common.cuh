@@ -86,7 +86,7 @@ struct SgbmPlan {
 #define SVB_LATENCY_MAX_BANDS 74    // 2 x 74 bands: both sweeps of a job this small fit the GPU's 148 SMs side by side
 
 // B: pairs processed together (decides the latency form: SgbmPlan::latency)
-int svb_make_plan(const svb_sgbm_params *raw, int H, int W, int ch, int B, SgbmPlan *plan);
+int svb_make_plan(const svb_sgbm_params *raw, int H, int W, int ch, int B, int latency_ok, SgbmPlan *plan);
 
 static inline size_t svb_align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 

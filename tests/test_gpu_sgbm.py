@@ -319,3 +319,29 @@ def test_workspace_guards_stay_intact(sv):
         got = out[GUARD:GUARD + B * H * W].reshape(B, H, W).cpu().numpy()
         for i, (l, r) in enumerate(pairs):
             assert np.array_equal(got[i], oracle.sgbm_compute(l, r, **kw)), (H, W, D, B, mode, i)
+
+
+def test_two_devices_in_one_process(sv):
+    """Several GPUs driven from one process ('8 threads with 8 contexts'): the per-device kernel
+    attributes (dynamic shared memory opt-in) must be set on every device.  Skipped on single-GPU boxes."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two visible GPUs")
+    L, R, kw = cases.full_inputs("c1")
+    ref = None
+    for dev in (0, 1, 0):
+        with torch.cuda.device(dev):
+            Ld, Rd = torch.from_numpy(L).to(f"cuda:{dev}"), torch.from_numpy(R).to(f"cuda:{dev}")
+            got = sv.StereoSGBM_create(**kw).compute(Ld, Rd)
+            assert got.device.index == dev
+            got = got.cpu().numpy()
+        ref = got if ref is None else ref
+        assert np.array_equal(got, ref)
+    D, H, W = 256, 60, 420
+    kw = synth.sgbm_kwargs(D, 5, 1)
+    l, r = synth.stereo_pair(H, W, D, seed=3)
+    want = oracle.sgbm_compute(l, r, **kw)
+    for dev in (1, 0):
+        with torch.cuda.device(dev):
+            assert np.array_equal(sv.StereoSGBM_create(**kw).compute(torch.from_numpy(l).to(f"cuda:{dev}"),
+                                                                     torch.from_numpy(r).to(f"cuda:{dev}")).cpu().numpy(), want)

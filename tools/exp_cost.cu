@@ -28,7 +28,7 @@ int main(int argc, char **argv)
     p.minDisparity = 0; p.numDisparities = D; p.blockSize = bs; p.P1 = 8 * ch * bs * bs; p.P2 = 32 * ch * bs * bs;
     p.disp12MaxDiff = 1; p.preFilterCap = 31; p.uniquenessRatio = 10; p.speckleWindowSize = 100; p.speckleRange = 2; p.mode = 1;
     SgbmPlan pl;
-    if (svb_make_plan(&p, H, W, ch, B, &pl)) { printf("plan: %s\n", svb_last_error()); return 1; }
+    if (svb_make_plan(&p, H, W, ch, B, 0, &pl)) { printf("plan: %s\n", svb_last_error()); return 1; }
     const size_t img = (size_t)H * W * ch;
     std::vector<uint8_t> hl(img * B), hr(img * B);
     uint32_t s = 12345;

@@ -9,6 +9,9 @@ int main(int argc, char **argv)
 #ifndef HNG
 #define HNG 15
 #endif
+#ifndef HMINB
+#define HMINB 0
+#endif
     const int NB = (H + HNG - 1) / HNG;
     const size_t vol = (size_t)H * W1 * Dp * 2, edge = (size_t)NB * W1 * 3 * Dp * 2;
     const size_t stride = ((2 * vol + edge + 4096 + (size_t)H * W * 6) + 255) / 256 * 256 + 256;
@@ -36,8 +39,8 @@ int main(int argc, char **argv)
             for (int b = 0; b < B; b++) cudaMemset(ws + b * stride + 2 * vol + edge, 0, 4096);
             a.ticket = tick; a.flip = pass; a.prog = (unsigned *)(ws + 2 * vol + edge) + pass * 512;
             cudaEventRecord(e0);
-            if (pass == 0) launch_sweep_t<4, 32, HNG, 3, false, true, false>(a, B * NB, 0);
-            else launch_sweep_t<4, 32, HNG, 3, true, true, false>(a, B * NB, 0);
+            if (pass == 0) launch_sweep_t<4, 32, HNG, 3, false, true, false, false, HMINB>(a, B * NB, 0);
+            else launch_sweep_t<4, 32, HNG, 3, true, true, false, true, HMINB>(a, B * NB, 0);
             cudaEventRecord(e1); cudaEventSynchronize(e1);
             float ms; cudaEventElapsedTime(&ms, e0, e1); if (ms < best) best = ms;
         }
