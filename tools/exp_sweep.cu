@@ -47,7 +47,7 @@ int main(int argc, char **argv)
         unsigned long long sp[4]; cudaMemcpyFromSymbol(sp, g_spin, sizeof sp); unsigned long long z[4] = {0,0,0,0}; cudaMemcpyToSymbol(g_spin, z, sizeof z);
         printf("   starved steps %.2f%% of consumer steps, spin cycles per consumer step %.1f\n", 100.0 * sp[0] / (sp[2] + 1), (double)sp[1] / (sp[2] + 1));
         cudaError_t e = cudaGetLastError();
-        const double steps = 1696.0 * B * NB / 148.0 / (HNG <= 8 ? 2 : 1);
+        const double steps = 1696.0 * B * NB / 148.0;
         printf("pass%d B=%d: %.3f ms  -> %.0f cycles/step @1.965GHz  (%s)\n", pass + 1, B, best, best * 1e-3 / steps * 1.965e9, cudaGetErrorString(e));
     }
     return 0;
