@@ -759,6 +759,8 @@ __global__ void __launch_bounds__(NGRP *G + (NV ? 32 : 0), MINB) k_sweep(const _
     if (PFD > 1) st.template prefetch_c<(1 < PFD ? 1 : 0), 1>();
     if (PFD > 2) st.template prefetch_c<(2 < PFD ? 2 : 0), 2>();
     if (PFD > 3) st.template prefetch_c<(3 < PFD ? 3 : 0), 3>();
+    if (PFD > 4) st.template prefetch_c<(4 < PFD ? 4 : 0), 4>();
+    if (PFD > 5) st.template prefetch_c<(5 < PFD ? 5 : 0), 5>();
     st.template prefetch_s<0, 0>();
     if (PFD > 1) st.template prefetch_s<(PFD > 1 ? 1 : 0), 1>();
 
@@ -796,7 +798,10 @@ static int launch_sweep_t(const AggArgs &a, int ngrid, cudaStream_t st)
 #ifndef AGG_PFD2
 #define AGG_PFD2 4
 #endif
-    constexpr int PFD = NR <= 4 ? (PASS2 ? AGG_PFD2 : 4) : 2;   // C prefetch depth in pixels (pass 2 is short of registers)
+#ifndef AGG_PFD1
+#define AGG_PFD1 6         // pass 1 has registers to spare (106 of 128): 6 pixels of C in flight instead of 4, 17.12 -> 16.89 ms
+#endif
+    constexpr int PFD = NR <= 4 ? (PASS2 ? AGG_PFD2 : AGG_PFD1) : 2;   // C prefetch depth in pixels (pass 2 is short of registers)
     const size_t smem = SweepSmem<NGRP, NV, PASS2>::bytes(a.Dp, 2 * NR);
     auto kern = k_sweep<NR, G, NGRP, NV, PASS2, SAFE, PAD, PFD, REV, MINB>;
     // the opt-in is per device and per function; setting it on every launch is cheap and stays correct with several
