@@ -203,9 +203,9 @@ def test_geometry_fuzz_vs_oracle(sv):
         for rep in range(2):
             ch = 3 if (rep == 1 and D <= 256) else 1
             minD = int(rng.choice([0, -16, 8]))
-            H = int(rng.integers(17, 40))
+            mode = int(rng.choice([0, 1, 2, 3]))
+            H = int(rng.integers(17, 40)) if mode != 2 else int(rng.integers(40, 75))   # (3WAY: stripes >= their overlap)
             W = D + abs(minD) + int(rng.choice([9, 23, 61, 64, 65, 127, 130]))
-            mode = int(rng.choice([0, 1, 3]))
             kw = dict(minDisparity=minD, numDisparities=D, blockSize=bs, P1=8 * ch * bs * bs, P2=32 * ch * bs * bs,
                       disp12MaxDiff=1, preFilterCap=31, uniquenessRatio=10, speckleWindowSize=20, speckleRange=2, mode=mode)
             if bs * bs * ch * (2 * 31 + 63) + kw["P2"] > 32767:
