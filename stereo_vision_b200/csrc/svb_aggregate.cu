@@ -63,7 +63,9 @@
                            // 6..16 measure the same, 32 is 1-2 % slower (lines evicted again), 0 is 11 % slower
 #endif
 #define AGG_PADE 8         // int16 elements of P2 halo in front of every ring vector
-// (Measured and not adopted: prefetch.global.L2 of the C / S streams 16 pixels ahead of the register prefetch — pass 2
+// (Measured and not adopted: a progress poll pipelined three barrier intervals deep instead of one — the staler value costs
+// more than the exposed load latency: single pair c3 3.58 -> 3.71 ms per pass, c1 0.93 -> 0.99 ms, pass 2 at B = 32 +4 %;
+// prefetch.global.L2 of the C / S streams 16 pixels ahead of the register prefetch — pass 2
 // 22.21 -> 21.89 ms in tools/exp_sweep.cu but 22.5 -> 23.7 ms in the product at B = 32, pass 1 16.90 -> 17.28 ms.)
 
 #ifdef EXP_HARNESS
